@@ -1,0 +1,294 @@
+// NCCL over NVLink replaces the reference's CUDA-aware MPI:
+//   * forward scatter of the input vector (DOLFINx Scatterer driven by scatter_fwd_begin/end with
+//     pack/unpack functors: src/vector.hpp:95-149, src/laplacian.hpp:286,320, src/cg.hpp:133-136)
+//     -> one pack kernel + grouped ncclSend/ncclRecv; ghosts are ordered by source rank, so each
+//     message is received straight into the ghost segment of the vector (no unpack kernel);
+//   * MPI_Allreduce of one scalar per dot product (src/vector.hpp:173, src/cg.hpp:76)
+//     -> ncclAllReduce on a double that never leaves device memory.
+// NCCL is resolved with dlopen at the first use so that single-GPU users need no NCCL at all and
+// the library binds to whichever libnccl the host process already loaded (e.g. torch's).
+#include "comm.cuh"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <mutex>
+
+#include "operator.cuh"
+
+namespace
+{
+struct NcclApi
+{
+  void* handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  std::string error;
+};
+
+NcclApi& nccl_api()
+{
+  static NcclApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names)
+    {
+      api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (api.handle)
+        break;
+    }
+    if (!api.handle)
+    {
+      api.error = std::string("cannot load libnccl: ") + dlerror();
+      return;
+    }
+#define LOAD(field, sym)                                                                           \
+  api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, sym));                       \
+  if (!api.field)                                                                                  \
+  {                                                                                                \
+    api.error = std::string("libnccl lacks ") + sym;                                               \
+    return;                                                                                        \
+  }
+    LOAD(GetUniqueId, "ncclGetUniqueId")
+    LOAD(CommInitRank, "ncclCommInitRank")
+    LOAD(CommDestroy, "ncclCommDestroy")
+    LOAD(AllReduce, "ncclAllReduce")
+    LOAD(Send, "ncclSend")
+    LOAD(Recv, "ncclRecv")
+    LOAD(GroupStart, "ncclGroupStart")
+    LOAD(GroupEnd, "ncclGroupEnd")
+    LOAD(GetErrorString, "ncclGetErrorString")
+#undef LOAD
+  });
+  return api;
+}
+
+int nccl_ready()
+{
+  NcclApi& api = nccl_api();
+  if (!api.error.empty())
+    return bd::fail(BD_ERR_NCCL, "%s", api.error.c_str());
+  return BD_SUCCESS;
+}
+
+#define BD_NCCL_CHECK(expr)                                                                        \
+  do                                                                                               \
+  {                                                                                                \
+    ncclResult_t bd_nr_ = (expr);                                                                  \
+    if (bd_nr_ != ncclSuccess)                                                                     \
+      return bd::fail(BD_ERR_NCCL, "%s:%d: NCCL reports %s for `%s`", __FILE__, __LINE__,          \
+                      nccl_api().GetErrorString(bd_nr_), #expr);                                   \
+  } while (0)
+} // namespace
+
+namespace bd
+{
+int allreduce_sum_f64(bd_comm* comm, double* buf, size_t count, cudaStream_t stream)
+{
+  if (!comm || comm->nranks == 1)
+    return BD_SUCCESS;
+  BD_NCCL_CHECK(nccl_api().AllReduce(buf, buf, count, ncclFloat64, ncclSum,
+                                     static_cast<ncclComm_t>(comm->nccl), stream));
+  return BD_SUCCESS;
+}
+} // namespace bd
+
+using namespace bd;
+
+extern "C" int bd_comm_unique_id(void* id_out)
+{
+  BD_REQUIRE(id_out, "bd_comm_unique_id: null argument");
+  static_assert(sizeof(ncclUniqueId) == BD_UNIQUE_ID_BYTES, "ncclUniqueId size");
+  BD_CHECK(nccl_ready());
+  BD_NCCL_CHECK(nccl_api().GetUniqueId(static_cast<ncclUniqueId*>(id_out)));
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_comm_create(const void* id, int rank, int nranks, bd_comm** out)
+{
+  BD_REQUIRE(out, "bd_comm_create: null argument");
+  *out = nullptr;
+  BD_REQUIRE(nranks >= 1 && rank >= 0 && rank < nranks, "bad rank / nranks");
+  auto c = new bd_comm;
+  c->rank = rank;
+  c->nranks = nranks;
+  if (cudaGetDevice(&c->device) != cudaSuccess)
+  {
+    delete c;
+    return fail(BD_ERR_CUDA, "cudaGetDevice failed");
+  }
+  if (nranks > 1)
+  {
+    if (!id)
+    {
+      delete c;
+      return fail(BD_ERR_INVALID_ARGUMENT, "bd_comm_create: null unique id");
+    }
+    int rc = nccl_ready();
+    if (rc != BD_SUCCESS)
+    {
+      delete c;
+      return rc;
+    }
+    ncclUniqueId uid;
+    memcpy(&uid, id, sizeof(uid));
+    ncclComm_t nc = nullptr;
+    ncclResult_t r = nccl_api().CommInitRank(&nc, nranks, uid, rank);
+    if (r != ncclSuccess)
+    {
+      delete c;
+      return fail(BD_ERR_NCCL, "ncclCommInitRank: %s", nccl_api().GetErrorString(r));
+    }
+    c->nccl = nc;
+  }
+  *out = c;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_comm_destroy(bd_comm* c)
+{
+  if (!c)
+    return BD_SUCCESS;
+  if (c->nccl)
+    nccl_api().CommDestroy(static_cast<ncclComm_t>(c->nccl));
+  delete c;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_halo_create(bd_comm* comm, int scalar_bits, int64_t n_owned, int64_t n_ghost,
+                              int n_send, const int32_t* send_ranks, const int64_t* send_counts,
+                              const int32_t* send_indices_host, int n_recv,
+                              const int32_t* recv_ranks, const int64_t* recv_counts, bd_halo** out)
+{
+  BD_REQUIRE(out && comm, "bd_halo_create: null argument");
+  *out = nullptr;
+  BD_REQUIRE(scalar_bits == 32 || scalar_bits == 64, "Invalid float size. Must be 32 or 64.");
+  BD_REQUIRE(n_owned >= 0 && n_ghost >= 0 && n_send >= 0 && n_recv >= 0, "negative size");
+  BD_REQUIRE(n_send == 0 || (send_ranks && send_counts && send_indices_host), "null send plan");
+  BD_REQUIRE(n_recv == 0 || (recv_ranks && recv_counts), "null receive plan");
+  auto h = new bd_halo;
+  auto bail = [&](int rc) {
+    bd_halo_destroy(h);
+    return rc;
+  };
+  h->comm = comm;
+  h->scalar_bits = scalar_bits;
+  h->n_owned = n_owned;
+  h->n_ghost = n_ghost;
+  std::int64_t tot = 0, rtot = 0;
+  for (int i = 0; i < n_send; ++i)
+  {
+    if (send_ranks[i] < 0 || send_ranks[i] >= comm->nranks || send_counts[i] < 0)
+      return bail(fail(BD_ERR_INVALID_ARGUMENT, "bad send plan entry %d", i));
+    h->send_ranks.push_back(send_ranks[i]);
+    h->send_counts.push_back(send_counts[i]);
+    tot += send_counts[i];
+  }
+  for (int i = 0; i < n_recv; ++i)
+  {
+    if (recv_ranks[i] < 0 || recv_ranks[i] >= comm->nranks || recv_counts[i] < 0)
+      return bail(fail(BD_ERR_INVALID_ARGUMENT, "bad receive plan entry %d", i));
+    h->recv_ranks.push_back(recv_ranks[i]);
+    h->recv_counts.push_back(recv_counts[i]);
+    rtot += recv_counts[i];
+  }
+  if (rtot != n_ghost)
+    return bail(fail(BD_ERR_INVALID_ARGUMENT, "receive counts (%lld) do not add up to n_ghost (%lld)",
+                     (long long)rtot, (long long)n_ghost));
+  for (std::int64_t i = 0; i < tot; ++i)
+    if (send_indices_host[i] < 0 || send_indices_host[i] >= n_owned)
+      return bail(fail(BD_ERR_INVALID_ARGUMENT, "send index %lld out of the owned range", (long long)i));
+  h->n_send_total = tot;
+  int rc;
+  if ((rc = h->send_idx.assign(send_indices_host, static_cast<size_t>(tot), false)) != BD_SUCCESS)
+    return bail(rc);
+  if ((rc = h->send_buf.alloc(static_cast<size_t>(tot > 0 ? tot : 1) * (scalar_bits / 8))) != BD_SUCCESS)
+    return bail(rc);
+  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess
+      || cudaEventCreateWithFlags(&h->ev_ready, cudaEventDisableTiming) != cudaSuccess
+      || cudaEventCreateWithFlags(&h->ev_done, cudaEventDisableTiming) != cudaSuccess)
+    return bail(fail(BD_ERR_CUDA, "halo stream/event creation failed"));
+  *out = h;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_halo_destroy(bd_halo* h)
+{
+  if (!h)
+    return BD_SUCCESS;
+  if (h->ev_ready)
+    cudaEventDestroy(h->ev_ready);
+  if (h->ev_done)
+    cudaEventDestroy(h->ev_done);
+  if (h->stream)
+    cudaStreamDestroy(h->stream);
+  delete h;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_halo_begin(bd_halo* h, void* x_dev, void* stream_)
+{
+  BD_REQUIRE(h && x_dev, "bd_halo_begin: null argument");
+  cudaStream_t stream = as_stream(stream_);
+  // the exchange starts once everything already queued on `stream` (the producer of x) is done
+  BD_CUDA_CHECK(cudaEventRecord(h->ev_ready, stream));
+  BD_CUDA_CHECK(cudaStreamWaitEvent(h->stream, h->ev_ready, 0));
+  if (h->comm->nranks > 1)
+  {
+    const size_t ts = static_cast<size_t>(h->scalar_bits / 8);
+    BD_CHECK(bd_pack(h->scalar_bits, h->n_send_total, h->send_idx.ptr, x_dev, h->send_buf.ptr, h->stream));
+    const ncclDataType_t dt = h->scalar_bits == 64 ? ncclFloat64 : ncclFloat32;
+    ncclComm_t nc = static_cast<ncclComm_t>(h->comm->nccl);
+    NcclApi& api = nccl_api();
+    BD_NCCL_CHECK(api.GroupStart());
+    std::int64_t off = 0;
+    for (size_t i = 0; i < h->send_ranks.size(); ++i)
+    {
+      BD_NCCL_CHECK(api.Send(h->send_buf.ptr + off * ts, static_cast<size_t>(h->send_counts[i]), dt,
+                             h->send_ranks[i], nc, h->stream));
+      off += h->send_counts[i];
+    }
+    char* ghost = static_cast<char*>(x_dev) + static_cast<size_t>(h->n_owned) * ts;
+    off = 0;
+    for (size_t i = 0; i < h->recv_ranks.size(); ++i)
+    {
+      BD_NCCL_CHECK(api.Recv(ghost + off * ts, static_cast<size_t>(h->recv_counts[i]), dt,
+                             h->recv_ranks[i], nc, h->stream));
+      off += h->recv_counts[i];
+    }
+    BD_NCCL_CHECK(api.GroupEnd());
+  }
+  BD_CUDA_CHECK(cudaEventRecord(h->ev_done, h->stream));
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_halo_end(bd_halo* h, void* stream)
+{
+  BD_REQUIRE(h, "bd_halo_end: null argument");
+  BD_CUDA_CHECK(cudaStreamWaitEvent(as_stream(stream), h->ev_done, 0));
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_laplacian_apply_halo(bd_laplacian* op, bd_halo* halo, void* in_dev, void* out_dev,
+                                       void* stream)
+{
+  if (!halo)
+    return bd_laplacian_apply(op, in_dev, out_dev, stream);
+  BD_REQUIRE(op, "bd_laplacian_apply_halo: null operator");
+  BD_REQUIRE(halo->n_owned + halo->n_ghost == op->ndofs && halo->scalar_bits == op->scalar_bits,
+             "halo plan does not match the operator");
+  // impl_operator (src/laplacian.hpp:281-349): begin scatter, lcells, end scatter, bcells
+  BD_CHECK(bd_halo_begin(halo, in_dev, stream));
+  BD_CHECK(bd_laplacian_apply_part(op, 0, in_dev, out_dev, stream));
+  BD_CHECK(bd_halo_end(halo, stream));
+  return bd_laplacian_apply_part(op, 1, in_dev, out_dev, stream);
+}

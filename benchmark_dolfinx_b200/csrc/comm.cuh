@@ -1,0 +1,34 @@
+// Inter-GPU plumbing: NCCL (loaded at run time with dlopen) + forward-scatter plan.
+#pragma once
+
+#include <vector>
+
+#include "common.cuh"
+
+struct bd_comm
+{
+  void* nccl = nullptr; // ncclComm_t
+  int rank = 0, nranks = 1;
+  int device = 0;
+};
+
+struct bd_halo
+{
+  bd_comm* comm = nullptr;
+  int scalar_bits = 64;
+  std::int64_t n_owned = 0, n_ghost = 0;
+  std::vector<int> send_ranks, recv_ranks;
+  std::vector<std::int64_t> send_counts, recv_counts;
+  std::int64_t n_send_total = 0;
+  bd::DeviceArray<std::int32_t> send_idx;
+  bd::DeviceArray<char> send_buf;
+  cudaStream_t stream = nullptr;      // exchange runs here, overlapped with the lcells kernel
+  cudaEvent_t ev_ready = nullptr;     // producer of x done
+  cudaEvent_t ev_done = nullptr;      // ghosts of x up to date
+};
+
+namespace bd
+{
+// sum-allreduce of `count` doubles in device memory, in place, stream-ordered
+int allreduce_sum_f64(bd_comm* comm, double* buf_dev, size_t count, cudaStream_t stream);
+} // namespace bd

@@ -1,0 +1,105 @@
+// Geometry-factor precompute for sm_100a.
+//
+// Replaces geometry_computation_gpu<T,Q> (reference src/geometry_gpu.hpp:26-132): for every
+// cell of a list and every quadrature point, J = sum_k x_k (x) grad phi_k, K = adj(J),
+// G = K K^T w / det J, six unique entries stored as planes of nq^3 per cell
+// (order 00,10,20,11,21,22), cell index = position in the list.
+//
+// Launch shape differs from the reference (one CTA per cell, nq^3 threads, which is 8..27
+// threads at low degree): the (cell, point) index space is flattened over 256-thread CTAs so
+// every warp is full and the six output planes are written as contiguous runs.  The kernel is
+// write-bandwidth bound (48 B or 24 B per point out, the 8 vertices of a cell are shared by
+// its nq^3 threads through L1).
+#include "common.cuh"
+
+namespace bd
+{
+template <typename T>
+__global__ void __launch_bounds__(256)
+    geometry_kernel(const T* __restrict__ xgeom, T* __restrict__ G,
+                    const std::int32_t* __restrict__ geometry_dofmap, const T* __restrict__ dphi,
+                    const T* __restrict__ weights, const std::int32_t* __restrict__ cells,
+                    std::int64_t ncells, int nq3)
+{
+  const std::int64_t total = ncells * nq3;
+  const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
+  for (std::int64_t idx = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+       idx < total; idx += stride)
+  {
+    const std::int64_t c = idx / nq3;
+    const int q = static_cast<int>(idx - c * nq3);
+    const std::int32_t* gd = geometry_dofmap + static_cast<std::int64_t>(cells[c]) * 8;
+    T J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+    {
+      const T* xk = xgeom + 3 * static_cast<std::int64_t>(__ldg(gd + k));
+      const T x0 = __ldg(xk), x1 = __ldg(xk + 1), x2 = __ldg(xk + 2);
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+      {
+        const T d = __ldg(dphi + (static_cast<std::int64_t>(j) * nq3 + q) * 8 + k);
+        J[0][j] += x0 * d;
+        J[1][j] += x1 * d;
+        J[2][j] += x2 * d;
+      }
+    }
+    // K = adj(J) = det(J) J^-1   (reference :100-108)
+    const T K00 = J[1][1] * J[2][2] - J[1][2] * J[2][1];
+    const T K01 = -J[0][1] * J[2][2] + J[0][2] * J[2][1];
+    const T K02 = J[0][1] * J[1][2] - J[0][2] * J[1][1];
+    const T K10 = -J[1][0] * J[2][2] + J[1][2] * J[2][0];
+    const T K11 = J[0][0] * J[2][2] - J[0][2] * J[2][0];
+    const T K12 = -J[0][0] * J[1][2] + J[0][2] * J[1][0];
+    const T K20 = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+    const T K21 = -J[0][0] * J[2][1] + J[0][1] * J[2][0];
+    const T K22 = J[0][0] * J[1][1] - J[0][1] * J[1][0];
+    const T detJ = J[0][0] * K00 - J[0][1] * K10 + J[0][2] * K20;
+    const T w = __ldg(weights + q);
+    T* g = G + c * (6 * static_cast<std::int64_t>(nq3)) + q;
+    g[0] = (K00 * K00 + K01 * K01 + K02 * K02) * w / detJ;
+    g[nq3] = (K10 * K00 + K11 * K01 + K12 * K02) * w / detJ;
+    g[2 * nq3] = (K20 * K00 + K21 * K01 + K22 * K02) * w / detJ;
+    g[3 * nq3] = (K10 * K10 + K11 * K11 + K12 * K12) * w / detJ;
+    g[4 * nq3] = (K20 * K10 + K21 * K11 + K22 * K12) * w / detJ;
+    g[5 * nq3] = (K20 * K20 + K21 * K21 + K22 * K22) * w / detJ;
+  }
+}
+
+template <typename T>
+int launch_geometry(int nq, const void* xgeom, const std::int32_t* gdofmap, const void* dphi,
+                    const void* weights, const std::int32_t* cells, std::int64_t ncells, void* G,
+                    cudaStream_t stream)
+{
+  const int nq3 = nq * nq * nq;
+  const std::int64_t total = ncells * nq3;
+  const std::int64_t want = (total + 255) / 256;
+  const std::int64_t cap = static_cast<std::int64_t>(sm_count()) * 8;
+  const int grid = static_cast<int>(want < cap ? want : cap);
+  geometry_kernel<T><<<grid, 256, 0, stream>>>(static_cast<const T*>(xgeom), static_cast<T*>(G),
+                                               gdofmap, static_cast<const T*>(dphi),
+                                               static_cast<const T*>(weights), cells, ncells, nq3);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+} // namespace bd
+
+extern "C" int bd_geometry_compute(int scalar_bits, int nq, const void* xgeom,
+                                   const int32_t* geometry_dofmap, const void* dphi_geometry,
+                                   const void* weights, const int32_t* cells, int64_t ncells,
+                                   void* G_out, void* stream)
+{
+  BD_REQUIRE(scalar_bits == 32 || scalar_bits == 64, "Invalid float size. Must be 32 or 64.");
+  if (nq < 2 || nq > 9)
+    return bd::fail(BD_ERR_UNSUPPORTED, "Unsupported degree [geometry]");
+  BD_REQUIRE(ncells >= 0, "negative cell count");
+  if (ncells == 0)
+    return BD_SUCCESS;
+  BD_REQUIRE(xgeom && geometry_dofmap && dphi_geometry && weights && cells && G_out,
+             "bd_geometry_compute: null pointer argument");
+  return scalar_bits == 64
+             ? bd::launch_geometry<double>(nq, xgeom, geometry_dofmap, dphi_geometry, weights, cells,
+                                           ncells, G_out, bd::as_stream(stream))
+             : bd::launch_geometry<float>(nq, xgeom, geometry_dofmap, dphi_geometry, weights, cells,
+                                          ncells, G_out, bd::as_stream(stream));
+}

@@ -1,0 +1,201 @@
+// bd_laplacian: replaces the host class MatFreeLaplacianGPU<T> of the reference
+// (src/laplacian.hpp:89-447): owns device copies of the mesh data, precomputes the geometry
+// tensor at construction and applies the operator cell list by cell list.
+#include "operator.cuh"
+#include "stiffness_launch.cuh"
+
+#include <cstring>
+
+using namespace bd;
+
+namespace
+{
+int check_device_available()
+{
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+  {
+    cudaGetLastError();
+    return fail(BD_ERR_NO_DEVICE, "no usable CUDA device (%s); this library has no CPU fallback",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  }
+  return BD_SUCCESS;
+}
+
+template <typename T>
+int fill_constants(bd_laplacian* op)
+{
+  // _cell_constants(num_cells, constant)  (src/laplacian.hpp:105); read by list position
+  const std::int64_t n = op->n_lcells + op->n_bcells;
+  BD_CHECK(op->cell_constants.alloc(static_cast<size_t>(n > 0 ? n : 1) * sizeof(T)));
+  return bd_set_value(op->scalar_bits, n, op->kappa, op->cell_constants.ptr, nullptr);
+}
+} // namespace
+
+extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** out)
+{
+  BD_REQUIRE(d && out, "bd_laplacian_create: null argument");
+  *out = nullptr;
+  BD_CHECK(check_device_available());
+  BD_REQUIRE(d->scalar_bits == 32 || d->scalar_bits == 64, "Invalid float size. Must be 32 or 64.");
+  if (d->degree < 1 || d->degree > 7)
+    return fail(BD_ERR_UNSUPPORTED, "Unsupported degree [operator]");
+  if (d->nq != d->degree + 1 && d->nq != d->degree + 2)
+    return fail(BD_ERR_UNSUPPORTED, "Unsupported nq");
+  if (d->nq == d->degree + 1 && !d->is_identity)
+    return fail(BD_ERR_UNSUPPORTED, "Expecting identity matrix for qmode=0");
+  if (d->nq == d->degree + 2 && d->is_identity)
+    return fail(BD_ERR_UNSUPPORTED, "identity interpolation with nq = degree + 2");
+  BD_REQUIRE(d->ncells >= 0 && d->ndofs >= 0 && d->nnodes >= 0 && d->n_lcells >= 0 && d->n_bcells >= 0,
+             "negative size in descriptor");
+  BD_REQUIRE(d->n_lcells + d->n_bcells <= d->ncells, "lcells + bcells exceed ncells");
+  BD_REQUIRE(d->ndofs <= 0x7fffffffLL && d->ncells <= 0x7fffffffLL,
+             "local dof / cell counts must fit int32 (as in the reference dofmap)");
+  const std::int64_t nd3 = static_cast<std::int64_t>(d->degree + 1) * (d->degree + 1) * (d->degree + 1);
+  BD_REQUIRE(d->ncells * nd3 <= 0x7fffffffLL * 4ll, "dofmap too large");
+  BD_REQUIRE(d->phi0 && d->dphi1 && d->weights && d->dphi_geometry, "null table pointer");
+
+  auto op = new bd_laplacian;
+  auto guard_fail = [&](int rc) {
+    delete op;
+    return rc;
+  };
+  op->scalar_bits = d->scalar_bits;
+  op->degree = d->degree;
+  op->nq = d->nq;
+  op->is_identity = d->is_identity != 0;
+  op->kappa = d->kappa;
+  op->ncells = d->ncells;
+  op->ndofs = d->ndofs;
+  op->nnodes = d->nnodes;
+  op->n_lcells = d->n_lcells;
+  op->n_bcells = d->n_bcells;
+  if (cudaGetDevice(&op->device) != cudaSuccess)
+    return guard_fail(fail(BD_ERR_CUDA, "cudaGetDevice failed"));
+  const bool borrow = (d->flags & BD_FLAG_BORROW_DEVICE_ARRAYS) != 0;
+  const size_t ts = op->scalar_size();
+  const int nq3 = d->nq * d->nq * d->nq;
+  int rc;
+#define TRY(expr)                                                                                  \
+  if ((rc = (expr)) != BD_SUCCESS)                                                                 \
+    return guard_fail(rc);
+  TRY(op->cell_dofmap.assign(d->cell_dofmap, static_cast<size_t>(d->ncells * nd3), borrow));
+  TRY(op->geometry_dofmap.assign(d->geometry_dofmap, static_cast<size_t>(d->ncells) * 8, borrow));
+  TRY(op->bc_marker.assign(d->bc_marker, static_cast<size_t>(d->ndofs), borrow));
+  TRY(op->xgeom.assign(static_cast<const char*>(d->xgeom), static_cast<size_t>(d->nnodes) * 3 * ts, borrow));
+  TRY(op->weights.assign(static_cast<const char*>(d->weights), static_cast<size_t>(nq3) * ts, false));
+  TRY(op->dphi_geometry.assign(static_cast<const char*>(d->dphi_geometry),
+                               static_cast<size_t>(3) * nq3 * 8 * ts, false));
+  // [lcells..., bcells...] in one list: G is indexed by position in it (src/laplacian.hpp:215-223)
+  const std::int64_t nlist = d->n_lcells + d->n_bcells;
+  TRY(op->cell_list.alloc(static_cast<size_t>(nlist > 0 ? nlist : 1)));
+  if (d->n_lcells > 0)
+  {
+    if (!d->lcells)
+      return guard_fail(fail(BD_ERR_INVALID_ARGUMENT, "null lcells"));
+    if (cudaMemcpy(op->cell_list.ptr, d->lcells, d->n_lcells * sizeof(std::int32_t), cudaMemcpyDefault)
+        != cudaSuccess)
+      return guard_fail(fail(BD_ERR_CUDA, "copy of lcells failed: %s", cudaGetErrorString(cudaGetLastError())));
+  }
+  if (d->n_bcells > 0)
+  {
+    if (!d->bcells)
+      return guard_fail(fail(BD_ERR_INVALID_ARGUMENT, "null bcells"));
+    if (cudaMemcpy(op->cell_list.ptr + d->n_lcells, d->bcells, d->n_bcells * sizeof(std::int32_t),
+                   cudaMemcpyDefault)
+        != cudaSuccess)
+      return guard_fail(fail(BD_ERR_CUDA, "copy of bcells failed: %s", cudaGetErrorString(cudaGetLastError())));
+  }
+  // tables: host copies (kernel launch parameter)
+  auto copy_table = [&](std::vector<char>& dst, const void* src, size_t bytes) -> int {
+    dst.resize(bytes);
+    BD_CUDA_CHECK(cudaMemcpy(dst.data(), src, bytes, cudaMemcpyDefault));
+    return BD_SUCCESS;
+  };
+  TRY(copy_table(op->phi0, d->phi0, static_cast<size_t>(d->nq) * (d->degree + 1) * ts));
+  TRY(copy_table(op->dphi1, d->dphi1, static_cast<size_t>(d->nq) * d->nq * ts));
+  TRY(d->scalar_bits == 64 ? fill_constants<double>(op) : fill_constants<float>(op));
+  // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272)
+  TRY(op->G.alloc(static_cast<size_t>(nlist > 0 ? nlist : 1) * 6 * nq3 * ts));
+  TRY(bd_geometry_compute(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                          op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, nlist, op->G.ptr,
+                          nullptr));
+  if (cudaDeviceSynchronize() != cudaSuccess) // device_synchronize()  (src/laplacian.hpp:224)
+    return guard_fail(fail(BD_ERR_CUDA, "geometry precompute failed: %s",
+                           cudaGetErrorString(cudaGetLastError())));
+#undef TRY
+  *out = op;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_laplacian_destroy(bd_laplacian* op)
+{
+  delete op;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_laplacian_geometry(bd_laplacian* op, const void** G_dev, int64_t* n_entries)
+{
+  BD_REQUIRE(op && G_dev && n_entries, "bd_laplacian_geometry: null argument");
+  *G_dev = op->G.ptr;
+  *n_entries = (op->n_lcells + op->n_bcells) * op->g_cell_stride();
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* in_dev, void* out_dev,
+                                       void* stream)
+{
+  BD_REQUIRE(op && in_dev && out_dev, "bd_laplacian_apply: null argument");
+  BD_REQUIRE(part == 0 || part == 1, "part must be 0 (zero + lcells) or 1 (bcells)");
+  BD_REQUIRE(in_dev != out_dev, "in and out must not alias");
+  const size_t ts = op->scalar_size();
+  StiffnessArgs a{};
+  a.u = in_dev;
+  a.y = out_dev;
+  a.dofmap = op->cell_dofmap.ptr;
+  a.bc = op->bc_marker.ptr;
+  a.phi0_host = op->phi0.data();
+  a.dphi1_host = op->dphi1.data();
+  a.stream = as_stream(stream);
+  if (part == 0)
+  {
+    // set_value(out, 0) over owned + ghost entries (src/laplacian.hpp:359)
+    BD_CUDA_CHECK(cudaMemsetAsync(out_dev, 0, static_cast<size_t>(op->ndofs) * ts, a.stream));
+    a.G = op->G.ptr;
+    a.cell_constants = op->cell_constants.ptr;
+    a.cells = op->cell_list.ptr;
+    a.ncells = op->n_lcells;
+  }
+  else
+  {
+    // geometry_ptr += 6 * Q^3 * lcells.size()  (src/laplacian.hpp:329)
+    a.G = op->G.ptr + static_cast<size_t>(op->n_lcells) * op->g_cell_stride() * ts;
+    a.cell_constants = op->cell_constants.ptr + static_cast<size_t>(op->n_lcells) * ts;
+    a.cells = op->cell_list.ptr + op->n_lcells;
+    a.ncells = op->n_bcells;
+  }
+  return stiffness_dispatch(op->scalar_bits, op->degree, op->nq, op->is_identity, a);
+}
+
+extern "C" int bd_laplacian_apply(bd_laplacian* op, const void* in_dev, void* out_dev, void* stream)
+{
+  BD_CHECK(bd_laplacian_apply_part(op, 0, in_dev, out_dev, stream));
+  return bd_laplacian_apply_part(op, 1, in_dev, out_dev, stream);
+}
+
+extern "C" int bd_laplacian_apply_host(bd_laplacian* op, const void* in_host, void* out_host)
+{
+  BD_REQUIRE(op && in_host && out_host, "bd_laplacian_apply_host: null argument");
+  const size_t bytes = static_cast<size_t>(op->ndofs) * op->scalar_size();
+  if (op->stage_in.count != bytes)
+  {
+    BD_CHECK(op->stage_in.alloc(bytes));
+    BD_CHECK(op->stage_out.alloc(bytes));
+  }
+  BD_CUDA_CHECK(cudaMemcpyAsync(op->stage_in.ptr, in_host, bytes, cudaMemcpyHostToDevice, nullptr));
+  BD_CHECK(bd_laplacian_apply(op, op->stage_in.ptr, op->stage_out.ptr, nullptr));
+  BD_CUDA_CHECK(cudaMemcpyAsync(out_host, op->stage_out.ptr, bytes, cudaMemcpyDeviceToHost, nullptr));
+  BD_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+  return BD_SUCCESS;
+}

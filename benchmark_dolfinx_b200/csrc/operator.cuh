@@ -1,0 +1,29 @@
+// Host-side operator object behind the opaque bd_laplacian handle.
+#pragma once
+
+#include <vector>
+
+#include "common.cuh"
+
+struct bd_laplacian
+{
+  int scalar_bits = 64;
+  int degree = 0, nq = 0;
+  bool is_identity = false;
+  double kappa = 0;
+  std::int64_t ncells = 0, ndofs = 0, nnodes = 0, n_lcells = 0, n_bcells = 0;
+  int device = 0;
+  // device data (owned or borrowed)
+  bd::DeviceArray<std::int32_t> cell_dofmap, geometry_dofmap, cell_list; // cell_list = [lcells.., bcells..]
+  bd::DeviceArray<std::int8_t> bc_marker;
+  bd::DeviceArray<char> xgeom, weights, dphi_geometry, G, cell_constants;
+  // 1-D tables on the host (they travel to the kernel as a launch parameter)
+  std::vector<char> phi0, dphi1;
+  // staging for bd_laplacian_apply_host
+  bd::DeviceArray<char> stage_in, stage_out;
+  // work vectors + scalars of bd_cg_solve, kept between calls
+  bd::DeviceArray<char> cg_work;
+  size_t scalar_size() const { return static_cast<size_t>(scalar_bits / 8); }
+  // offset (in entries of T) of the bcells part of G
+  std::int64_t g_cell_stride() const { return 6ll * nq * nq * nq; }
+};

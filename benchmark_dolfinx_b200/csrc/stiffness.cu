@@ -1,0 +1,43 @@
+// Dispatch + C entry point for the stiffness kernel.
+#include "stiffness_launch.cuh"
+
+namespace bd
+{
+int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const StiffnessArgs& a)
+{
+  if (scalar_bits != 32 && scalar_bits != 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "Invalid float size. Must be 32 or 64.");
+  if (degree < 1 || degree > 7)
+    return fail(BD_ERR_UNSUPPORTED, "Unsupported degree [operator]");
+  if (nq == degree + 1)
+  {
+    if (!identity)
+      return fail(BD_ERR_UNSUPPORTED, "Expecting identity matrix for qmode=0");
+    return scalar_bits == 64 ? launch_stiffness_f64_q0(degree, a) : launch_stiffness_f32_q0(degree, a);
+  }
+  if (nq == degree + 2)
+  {
+    if (identity)
+      return fail(BD_ERR_UNSUPPORTED, "identity interpolation with nq = degree + 2");
+    return scalar_bits == 64 ? launch_stiffness_f64_q1(degree, a) : launch_stiffness_f32_q1(degree, a);
+  }
+  return fail(BD_ERR_UNSUPPORTED, "Unsupported nq");
+}
+} // namespace bd
+
+extern "C" int bd_stiffness_apply(int scalar_bits, int degree, int nq, int is_identity,
+                                  const void* in, const void* cell_constants, void* out,
+                                  const void* G, const void* phi0_host, const void* dphi1_host,
+                                  const int32_t* cell_dofmap, const int32_t* cells, int64_t ncells,
+                                  const int8_t* bc_marker, void* stream)
+{
+  BD_REQUIRE(ncells >= 0, "negative cell count");
+  if (ncells == 0)
+    return BD_SUCCESS;
+  BD_REQUIRE(in && out && G && cell_constants && phi0_host && dphi1_host && cell_dofmap && cells
+                 && bc_marker,
+             "bd_stiffness_apply: null pointer argument");
+  bd::StiffnessArgs a{in,     out,       G,         cell_constants, cell_dofmap, cells,
+                      ncells, bc_marker, phi0_host, dphi1_host,     bd::as_stream(stream)};
+  return bd::stiffness_dispatch(scalar_bits, degree, nq, is_identity != 0, a);
+}

@@ -1,0 +1,317 @@
+// Sum-factorised Q_k hexahedral stiffness action for sm_100a.
+//
+// Replaces stiffness_operator_gpu<T,P,Q> (reference src/laplacian_gpu.hpp:91-426).
+// Same mathematics and the same data contract (u, dofmap, G by list position, BC
+// markers, phi0/dphi1 tables), different execution model:
+//
+//  * a thread owns a whole x-column of a cell (NQ values in registers), the
+//    (y,z) plane of the cell is spread over NQ*NQ threads, and several cells share
+//    one CTA.  The x-direction contractions run entirely in registers with the
+//    1-D tables read as constant-bank operands of the FMA (the tables travel as a
+//    __grid_constant__ kernel parameter); only the y and z contractions exchange
+//    data through shared memory.  The reference uses one thread per quadrature
+//    point and goes through shared memory for every operand of every FMA.
+//  * CTAs are persistent: the grid is a multiple of the SM count and each CTA
+//    strides over batches of cells, so the G stream (90 % of the bytes) is read
+//    with fully coalesced, contiguous accesses per (cell, q0) slice.
+//  * results are scattered with red.global.add (no return value needed).
+#pragma once
+
+#include <cstdint>
+
+namespace bd
+{
+
+template <typename T, int ND, int NQ>
+struct Tables1D
+{
+  T phi[NQ * ND];  // phi0[q][i]   (identity when ND == NQ and qmode 0)
+  T dphi[NQ * NQ]; // dphi1[q][i]
+};
+
+// cells per CTA for a given NQ: fill ~128 threads
+constexpr int cells_per_block(int nq)
+{
+  int c = 128 / (nq * nq);
+  return c < 1 ? 1 : c;
+}
+constexpr int block_threads(int nq)
+{
+  int t = cells_per_block(nq) * nq * nq;
+  return ((t + 31) / 32) * 32;
+}
+
+template <typename T>
+__device__ __forceinline__ void red_add(T* addr, T v)
+{
+  atomicAdd(addr, v); // result unused -> RED.E.ADD.F32/F64
+}
+
+// One x-column per thread.  IDENTITY: qmode 0 (phi0 is the identity, ND == NQ).
+template <typename T, int P, int NQ, bool IDENTITY>
+__global__ void __launch_bounds__(block_threads(NQ))
+    stiffness_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ G,
+                     const T* __restrict__ cell_constants, const std::int32_t* __restrict__ dofmap,
+                     const std::int32_t* __restrict__ cells, int ncells,
+                     const std::int8_t* __restrict__ bc,
+                     const __grid_constant__ Tables1D<T, P + 1, NQ> tab)
+{
+  constexpr int ND = P + 1;
+  constexpr int CPB = cells_per_block(NQ);
+  constexpr int NQ2 = NQ * NQ;
+  constexpr int NQ3 = NQ2 * NQ;
+  constexpr int ND2 = ND * ND;
+  constexpr int ND3 = ND2 * ND;
+  constexpr int ZP = NQ + ((NQ % 2 == 0) ? 1 : 0); // padded z extent (bank conflicts)
+  constexpr int SLAB = NQ * NQ * ZP;
+
+  __shared__ T sA[CPB * SLAB];
+  __shared__ T sB[CPB * SLAB];
+  __shared__ T sC[CPB * SLAB];
+
+  const int tid = threadIdx.x;
+  const int slot = tid / NQ2;      // cell within the CTA
+  const int rem = tid - slot * NQ2;
+  const int a = rem / NQ;          // y index (dof j / point q1)
+  const int b = rem - a * NQ;      // z index (dof k / point q2)
+  const bool lane_ok = slot < CPB; // padding threads only take part in barriers
+  T* A = sA + (lane_ok ? slot : 0) * SLAB;
+  T* B = sB + (lane_ok ? slot : 0) * SLAB;
+  T* C = sC + (lane_ok ? slot : 0) * SLAB;
+  auto at = [](int x, int yy, int z) { return (x * NQ + yy) * ZP + z; };
+
+  const int nbatches = (ncells + CPB - 1) / CPB;
+  for (int batch = blockIdx.x; batch < nbatches; batch += gridDim.x)
+  {
+    const int pos = batch * CPB + slot; // position in the cell list (indexes G, constants)
+    const bool active = lane_ok && pos < ncells;
+    const bool dof_thread = active && a < ND && b < ND;
+
+    // ---- gather the x-column of dofs (reference :153-170)
+    int dof[ND];
+    T col[NQ];
+#pragma unroll
+    for (int i = 0; i < NQ; ++i)
+      col[i] = 0;
+    if (dof_thread)
+    {
+      const std::int32_t* row = dofmap + static_cast<std::int64_t>(cells[pos]) * ND3 + a * ND + b;
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+        dof[i] = row[i * ND2];
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+      {
+        const T v = u[dof[i]];
+        if (bc[dof[i]])
+        {
+          y[dof[i]] = v; // b[dof] = u[dof] on constrained dofs
+          dof[i] = -1;
+        }
+        else
+          col[i] = v;
+      }
+    }
+
+    if constexpr (!IDENTITY)
+    {
+      // ---- interpolate dofs -> quadrature points (reference :175-211)
+      // x direction: registers only
+      T t[NQ];
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+      {
+        T s = 0;
+#pragma unroll
+        for (int i = 0; i < ND; ++i)
+          s += tab.phi[q * ND + i] * col[i];
+        t[q] = s;
+      }
+      if (dof_thread)
+      {
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+          A[at(q, a, b)] = t[q];
+      }
+      __syncthreads();
+      // y direction: thread (q1 = a, k = b < ND)
+      if (active && b < ND)
+      {
+        T pr[ND];
+#pragma unroll
+        for (int j = 0; j < ND; ++j)
+          pr[j] = tab.phi[a * ND + j];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+        {
+          T s = 0;
+#pragma unroll
+          for (int j = 0; j < ND; ++j)
+            s += pr[j] * A[at(q, j, b)];
+          B[at(q, a, b)] = s;
+        }
+      }
+      __syncthreads();
+      // z direction: thread (q1 = a, q2 = b)
+      if (active)
+      {
+        T pr[ND];
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+          pr[k] = tab.phi[b * ND + k];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+        {
+          T s = 0;
+#pragma unroll
+          for (int k = 0; k < ND; ++k)
+            s += pr[k] * B[at(q, a, k)];
+          col[q] = s;
+        }
+      }
+    }
+
+    // ---- col[q0] now holds u at the quadrature points (q0, a, b)
+    if (active)
+    {
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        A[at(q, a, b)] = col[q];
+    }
+    __syncthreads();
+
+    T fx[NQ];
+    if (active)
+    {
+      // reference gradient (reference :239-251) and geometry (reference :256-273)
+      T dy[NQ], dz[NQ];
+#pragma unroll
+      for (int i = 0; i < NQ; ++i)
+      {
+        dy[i] = tab.dphi[a * NQ + i];
+        dz[i] = tab.dphi[b * NQ + i];
+      }
+      const T kappa = cell_constants[pos];
+      const T* Gc = G + static_cast<std::int64_t>(pos) * (6 * NQ3) + a * NQ + b;
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+      {
+        const T G0 = __ldg(Gc + 0 * NQ3 + q * NQ2);
+        const T G1 = __ldg(Gc + 1 * NQ3 + q * NQ2);
+        const T G2 = __ldg(Gc + 2 * NQ3 + q * NQ2);
+        const T G3 = __ldg(Gc + 3 * NQ3 + q * NQ2);
+        const T G4 = __ldg(Gc + 4 * NQ3 + q * NQ2);
+        const T G5 = __ldg(Gc + 5 * NQ3 + q * NQ2);
+        T gx = 0, gy = 0, gz = 0;
+#pragma unroll
+        for (int i = 0; i < NQ; ++i)
+        {
+          gx += tab.dphi[q * NQ + i] * col[i];
+          gy += dy[i] * A[at(q, i, b)];
+          gz += dz[i] * A[at(q, a, i)];
+        }
+        fx[q] = kappa * (G0 * gx + G1 * gy + G2 * gz);
+        B[at(q, a, b)] = kappa * (G1 * gx + G3 * gy + G4 * gz);
+        C[at(q, a, b)] = kappa * (G2 * gx + G4 * gy + G5 * gz);
+      }
+    }
+    __syncthreads();
+
+    // ---- transposed gradient (reference :307-314)
+    if (active)
+    {
+      T dty[NQ], dtz[NQ];
+#pragma unroll
+      for (int i = 0; i < NQ; ++i)
+      {
+        dty[i] = tab.dphi[i * NQ + a];
+        dtz[i] = tab.dphi[i * NQ + b];
+      }
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+      {
+        T s = 0;
+#pragma unroll
+        for (int i = 0; i < NQ; ++i)
+        {
+          s += tab.dphi[i * NQ + q] * fx[i];
+          s += dty[i] * B[at(q, i, b)];
+          s += dtz[i] * C[at(q, a, i)];
+        }
+        col[q] = s;
+      }
+    }
+
+    if constexpr (!IDENTITY)
+    {
+      // ---- interpolate back quadrature points -> dofs (reference :388-420)
+      // x direction in registers
+      T w[ND];
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+      {
+        T s = 0;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+          s += tab.phi[q * ND + i] * col[q];
+        w[i] = s;
+      }
+      if (active)
+      {
+#pragma unroll
+        for (int i = 0; i < ND; ++i)
+          A[at(i, a, b)] = w[i];
+      }
+      __syncthreads();
+      // y direction: thread (j = a < ND, q2 = b)
+      if (active && a < ND)
+      {
+        T pc[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+          pc[q] = tab.phi[q * ND + a];
+#pragma unroll
+        for (int i = 0; i < ND; ++i)
+        {
+          T s = 0;
+#pragma unroll
+          for (int q = 0; q < NQ; ++q)
+            s += pc[q] * A[at(i, q, b)];
+          B[at(i, a, b)] = s;
+        }
+      }
+      __syncthreads();
+      // z direction: thread (j = a < ND, k = b < ND)
+      if (dof_thread)
+      {
+        T pc[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+          pc[q] = tab.phi[q * ND + b];
+#pragma unroll
+        for (int i = 0; i < ND; ++i)
+        {
+          T s = 0;
+#pragma unroll
+          for (int q = 0; q < NQ; ++q)
+            s += pc[q] * B[at(i, a, q)];
+          col[i] = s;
+        }
+      }
+    }
+
+    // ---- scatter-add (reference :424-425)
+    if (dof_thread)
+    {
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+        if (dof[i] >= 0)
+          red_add(y + dof[i], col[i]);
+    }
+    // No barrier needed here: the next iteration's first shared-memory write (A)
+    // is ordered after every read of A of this iteration by the barriers above,
+    // and B/C are rewritten only after the next iteration's first barrier.
+  }
+}
+
+} // namespace bd

@@ -1,0 +1,38 @@
+// Instantiation unit: compiled four times with -DBD_INST_T={double,float} -DBD_INST_QMODE={0,1}.
+#include "stiffness_launch.cuh"
+
+#ifndef BD_INST_T
+#error "define BD_INST_T, BD_INST_SUFFIX and BD_INST_QMODE"
+#endif
+
+#define BD_CAT_(a, b, c) a##b##_q##c
+#define BD_CAT(a, b, c) BD_CAT_(a, b, c)
+
+namespace bd
+{
+#if BD_INST_QMODE == 0
+#define BD_CASE(P)                                                                                 \
+  case P:                                                                                          \
+    return launch_stiffness<BD_INST_T, P, P + 1, true>(a);
+#else
+#define BD_CASE(P)                                                                                 \
+  case P:                                                                                          \
+    return launch_stiffness<BD_INST_T, P, P + 2, false>(a);
+#endif
+
+int BD_CAT(launch_stiffness_, BD_INST_SUFFIX, BD_INST_QMODE)(int degree, const StiffnessArgs& a)
+{
+  switch (degree)
+  {
+    BD_CASE(1)
+    BD_CASE(2)
+    BD_CASE(3)
+    BD_CASE(4)
+    BD_CASE(5)
+    BD_CASE(6)
+    BD_CASE(7)
+  default:
+    return fail(BD_ERR_UNSUPPORTED, "Unsupported degree [operator]");
+  }
+}
+} // namespace bd

@@ -1,0 +1,74 @@
+// Host-side launcher shared by the per-(scalar, qmode) instantiation units.
+#pragma once
+
+#include "common.cuh"
+#include "stiffness.cuh"
+
+namespace bd
+{
+struct StiffnessArgs
+{
+  const void* u;
+  void* y;
+  const void* G;
+  const void* cell_constants;
+  const std::int32_t* dofmap;
+  const std::int32_t* cells;
+  std::int64_t ncells;
+  const std::int8_t* bc;
+  const void* phi0_host;  // T[nq*nd]
+  const void* dphi1_host; // T[nq*nq]
+  cudaStream_t stream;
+};
+
+template <typename T, int P, int NQ, bool IDENTITY>
+int launch_stiffness(const StiffnessArgs& a)
+{
+  constexpr int ND = P + 1;
+  constexpr int CPB = cells_per_block(NQ);
+  constexpr int THREADS = block_threads(NQ);
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  auto kernel = stiffness_kernel<T, P, NQ, IDENTITY>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, THREADS, 0));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  Tables1D<T, ND, NQ> tab;
+  const T* phi = static_cast<const T*>(a.phi0_host);
+  const T* dphi = static_cast<const T*>(a.dphi1_host);
+  for (int i = 0; i < NQ * ND; ++i)
+    tab.phi[i] = phi[i];
+  for (int i = 0; i < NQ * NQ; ++i)
+    tab.dphi[i] = dphi[i];
+  const std::int64_t nbatches = (a.ncells + CPB - 1) / CPB;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(nbatches < max_grid ? nbatches : max_grid);
+  kernel<<<grid, THREADS, 0, a.stream>>>(
+      static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
+      static_cast<const T*>(a.cell_constants), a.dofmap, a.cells, static_cast<int>(a.ncells), a.bc,
+      tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+// One function per (scalar, qmode), each defined in its own translation unit so
+// the 28 kernel instantiations compile in parallel.
+int launch_stiffness_f64_q0(int degree, const StiffnessArgs& a);
+int launch_stiffness_f64_q1(int degree, const StiffnessArgs& a);
+int launch_stiffness_f32_q0(int degree, const StiffnessArgs& a);
+int launch_stiffness_f32_q1(int degree, const StiffnessArgs& a);
+
+// Dispatch on (scalar_bits, degree, nq, identity); mirrors the reference's
+// dispatch and its error strings (src/laplacian.hpp:361-400).
+int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const StiffnessArgs& a);
+} // namespace bd
