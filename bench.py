@@ -1,0 +1,414 @@
+#!/usr/bin/env python
+"""Headline benchmark: GDoF/s of the matrix-free Laplacian action (and CG iteration).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (CUDA, one rank per GPU)
+    python bench.py --impl reference --gpus N --steps K ...  # reference CPU kernels on host cores
+
+A "step" is one operator application y = A u (src/laplacian.hpp:355-403) over the whole local
+mesh; the metric is the reference's own `ndofs_global * nreps / (1e9 * seconds)`
+(src/main.cpp:129-130).  Default workload: BASELINE.json's headline configuration, Q3, qmode 1
+(GLL), fp64, 300M dofs per GPU on the `compute_mesh_size` box (weak scaling: the global box is
+re-derived from ndofs x ranks exactly as src/main.cpp:237-238,272-273 does).  The same run also
+times `steps` CG iterations (src/cg.hpp:89-169) and reports them under "cg".
+
+Rank 0 prints ONE JSON line.  Timing: CUDA events on the launching stream, barrier +
+synchronize on both sides, max over ranks.  The inputs (G alone is 66 GB) are far larger than
+the 126 MB L2, so no explicit L2 flush is needed between iterations.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+# ----------------------------------------------------------------------------- byte / flop model
+def algorithmic_bytes_per_apply(ndofs_local, ncells, degree, nq, tsize):
+    """SURVEY.md section 8(d), variant "G precomputed": read u + write y once (2T per dof),
+    dofmap (4 nd^3 per cell), G (6 T nq^3 per cell), BC marker (1 per dof)."""
+    nd3 = (degree + 1) ** 3
+    return 2 * tsize * ndofs_local + 4 * nd3 * ncells + 6 * tsize * nq ** 3 * ncells + ndofs_local
+
+
+def algorithmic_flops_per_cell(degree, nq, qmode):
+    nd = degree + 1
+    return 2 * (2 * (nq * nd ** 3 + nq ** 2 * nd ** 2 + nq ** 3 * nd)) * qmode + 12 * nq ** 4 + 18 * nq ** 3
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        self.proc, self.lines = None, []
+        sel = str(device_index)
+        try:
+            import torch
+            uuid = getattr(torch.cuda.get_device_properties(device_index), "uuid", None)
+            if uuid is not None:
+                sel = "GPU-" + str(uuid)
+        except Exception:
+            pass
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if not sel.startswith("GPU-") and vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if device_index < len(ids):
+                sel = ids[device_index]
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", sel, f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                smax.append(float(parts[1]))
+                power.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(smax), "power_w_max": max(power),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def cpu_reference_run(degree, bits, steps, warmup, target_seconds, cells_per_dim=None):
+    """The reference's own CPU implementation of the path (oracle/_ref: unmodified
+    stiffness_operator_cpu, src/laplacian_cpu.hpp:57-146; qmode 0 is all it supports) on every
+    host core: one independent instance per core on its own sub-box, which emulates the
+    reference's `mpirun -n <cores>` (one single-threaded rank per core) without halo cost.
+    Falls back to the plain-C port (oracle/port.c) when oracle/_ref is absent.
+    Returns (GDoF/s, cores, kind, sample description, steps run, seconds)."""
+    from oracle import native
+    from oracle.boxmesh import create_box_mesh
+    from oracle.tables import Tables
+    dt = np.float64 if bits == 64 else np.float32
+    ref = native.ref_lib(False)
+    port = native.port_lib()
+    kind = "reference" if ref is not None else "port"
+    if ref is None and port is None:
+        raise RuntimeError("neither oracle/_ref nor oracle/libport.so is built")
+    cores = os.cpu_count() or 1
+    qmode = 0
+    t = Tables(degree, qmode)
+    nc = cells_per_dim or max(2, int(round((24 ** 3 * 27 / degree ** 3) ** (1 / 3))))
+    mesh = create_box_mesh([nc, nc, nc], degree)
+    cells = np.concatenate([mesh.lcells, mesh.bcells]).astype(np.int32)
+    xg = mesh.xgeom.astype(dt)
+    dphi, w = t.dphi_geometry.astype(dt), t.weights3d.astype(dt)
+    phi0, dphi1 = t.phi0.astype(dt), t.dphi1.astype(dt)
+    if ref is not None:
+        G = native.ref_geometry(ref, t.nq, xg, mesh.geometry_dofmap, dphi, w, cells)
+    else:
+        G = native.port_geometry(port, t.nq, xg, mesh.geometry_dofmap, dphi, w, cells)
+    consts = np.full(mesh.ncells, 2.0, dtype=dt)
+    rng = np.random.default_rng(1234)
+    insts = []
+    for _ in range(cores):   # private copies: every emulated rank streams its own arrays
+        insts.append(dict(u=rng.uniform(-1, 1, mesh.ndofs_local).astype(dt),
+                          y=np.zeros(mesh.ndofs_local, dtype=dt), G=G.copy(),
+                          dm=mesh.cell_dofmap.copy()))
+
+    def one_apply(inst):
+        inst["y"][:] = 0
+        if ref is not None:
+            native.ref_stiffness(ref, degree, inst["u"], inst["y"], inst["G"], consts, phi0, dphi1,
+                                 inst["dm"], cells, mesh.bc_marker)
+        else:
+            native.port_stiffness(port, t.nd, t.nq, True, inst["u"], inst["y"], inst["G"], consts,
+                                  phi0, dphi1, inst["dm"], cells, mesh.bc_marker)
+
+    def run_steps(nsteps):
+        def work(inst):
+            for _ in range(nsteps):
+                one_apply(inst)
+        th = [threading.Thread(target=work, args=(i,)) for i in insts]
+        t0 = time.perf_counter()
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        return time.perf_counter() - t0
+
+    t1 = run_steps(max(1, warmup))           # warm-up, also calibrates the step count
+    per_step = t1 / max(1, warmup)
+    if target_seconds is not None:
+        steps = max(1, min(steps, int(target_seconds / max(per_step, 1e-9))))
+    secs = run_steps(steps)
+    gdofs = mesh.ndofs_global * cores * steps / (1e9 * secs)
+    sample = (f"{cores} independent instances (one per core) of a {nc}x{nc}x{nc}-cell Q{degree} box, "
+              f"{mesh.ndofs_global} dofs each, qmode 0 (the reference CPU kernel has no qmode 1), "
+              f"fp{bits}, {steps} applies each, {kind} kernel built -O3 -ffast-math")
+    return gdofs, cores, kind, sample, steps, secs
+
+
+def run_reference_arm(args, rank):
+    if rank != 0:
+        return
+    gdofs, cores, kind, sample, steps, secs = cpu_reference_run(
+        args.degree, args.float, args.steps, args.warmup, target_seconds=120.0)
+    line = {
+        "impl": "reference", "metric": "gdof_per_second_laplacian_action", "value": gdofs,
+        "unit": "GDoF/s", "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * secs / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": gdofs, "unit": "GDoF/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": gdofs, "unit": "GDoF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world):
+    return {
+        "workload": (f"Q{args.degree} matrix-free Laplacian action, qmode {args.qmode} (GLL), fp{args.float}, "
+                     f"{args.ndofs} dofs per GPU on the compute_mesh_size unit-cube hex box, kappa=2, "
+                     "u = assembled RHS of src/main.cpp:81-92"),
+        "degree": args.degree, "qmode": args.qmode, "ndofs_per_gpu": args.ndofs,
+        "partition": {1: "1x1x1", 2: "2x1x1", 4: "2x2x1", 8: "2x2x2"}.get(world, f"{world} ranks"),
+        "l2": "inputs (G, dofmap, vectors) are >100x larger than the 126 MB L2; no flush needed",
+    }
+
+
+# ----------------------------------------------------------------------------- our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--degree", type=int, default=3)
+    ap.add_argument("--ndofs", type=int, default=300_000_000, help="dofs per GPU (reference --ndofs)")
+    ap.add_argument("--float", type=int, default=64, choices=[32, 64])
+    ap.add_argument("--qmode", type=int, default=1, choices=[0, 1])
+    ap.add_argument("--no-cg", action="store_true", help="skip the CG leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import benchmark_dolfinx_b200 as bd
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    comm = bd.Comm.from_torch_distributed() if world > 1 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    dtype = np.float64 if args.float == 64 else np.float32
+    tsize = args.float // 8
+    degree, qmode = args.degree, args.qmode
+    n = bd.compute_mesh_size(args.ndofs * world, degree)           # src/main.cpp:237-238,272-273
+    t_setup = time.perf_counter()
+    mesh = bd.BoxMesh(n, degree, rank, world, dtype=dtype)
+    halo = bd.Halo(comm, mesh) if world > 1 else None
+    op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, halo=halo)
+    u = mesh.assemble_rhs(qmode)
+    y = torch.zeros_like(u)
+    if halo is not None:
+        halo.scatter_fwd(u)
+    torch.cuda.synchronize()
+    t_setup = time.perf_counter() - t_setup
+    ndofs_global = mesh.ndofs_global
+    nq = degree + 1 + qmode
+
+    # ---- operator action: W warm-up + K timed steps
+    for _ in range(args.warmup):
+        op.apply(u, y)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    op.profile(True)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        op.apply(u, y)
+    ev1.record()
+    barrier()
+    secs = max_over_ranks(ev0.elapsed_time(ev1) / 1e3)
+    kernel_ms, kernel_launches = op.profile_read()
+    op.profile(False)
+    clocks = sampler.stop() if sampler is not None else None
+    value = ndofs_global * args.steps / (1e9 * secs)
+    unorm = bd.norm(u, mesh.ndofs_owned, comm)
+    ynorm = bd.norm(y, mesh.ndofs_owned, comm)
+
+    # ---- roofline of the dominant kernel (stiffness), from the per-launch events
+    peak, peak_src = measured_peak_gbs()
+    bytes_apply = algorithmic_bytes_per_apply(mesh.ndofs_local, mesh.ncells, degree, nq, tsize)
+    kernel_s_per_apply = max_over_ranks(kernel_ms / 1e3 / args.steps)
+    achieved = bytes_apply / kernel_s_per_apply / 1e9
+    launches_per_apply = kernel_launches // args.steps
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            tr = json.load(f)
+        key = f"q{degree}_qmode{qmode}_f{args.float}"
+        if key in tr and tr[key].get("ncells"):
+            traffic = tr[key]["dram_bytes_per_launch"] * (mesh.ncells / tr[key]["ncells"])
+    except Exception:
+        pass
+    roofline = {
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
+        "kernel": f"bd::stiffness_kernel<{'double' if args.float == 64 else 'float'},{degree},{nq}>",
+        "kernel_ms_per_apply": 1e3 * kernel_s_per_apply, "kernel_launches_per_apply": launches_per_apply,
+        "algorithmic_bytes_per_apply": bytes_apply,
+        "algorithmic_bytes_per_dof": bytes_apply / mesh.ndofs_local,
+        "fp_gflops_algorithmic": algorithmic_flops_per_cell(degree, nq, qmode) * mesh.ncells
+                                 / kernel_s_per_apply / 1e9,
+    }
+
+    # ---- CG: `steps` iterations (timed region includes the initial apply, as src/cg.hpp:108)
+    cg = None
+    gpu_launches = args.steps * launches_per_apply + (args.steps if world > 1 else 0)
+    if not args.no_cg:
+        x = torch.zeros_like(u)
+        bd.cg_solve(op, x, u, max(1, args.warmup), 0.0, comm)
+        barrier()
+        x.zero_()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        its = bd.cg_solve(op, x, u, args.steps, 0.0, comm)
+        c1.record()
+        barrier()
+        cg_secs = max_over_ranks(c0.elapsed_time(c1) / 1e3)
+        cg_bytes = bytes_apply + 11 * tsize * mesh.ndofs_local   # SURVEY.md 8(d) CG add-on
+        cg = {"value": ndofs_global * its / (1e9 * cg_secs), "unit": "GDoF/s", "iterations": its,
+              "ms_per_iter": 1e3 * cg_secs / its, "x_norm": bd.norm(x, mesh.ndofs_owned, comm),
+              "hbm_gbs_algorithmic": cg_bytes * (its + 1) / its / cg_secs / 1e9,
+              "note": "timed region = initial apply + iterations, as the reference's cg_solve"}
+        del x
+
+    # ---- end to end through the host-buffer C-ABI call: H2D u, (halo +) apply, D2H y every step
+    e2e = None
+    if not args.no_e2e:
+        uh = torch.empty(mesh.ndofs_local, dtype=u.dtype, pin_memory=True)
+        yh = torch.empty(mesh.ndofs_local, dtype=u.dtype, pin_memory=True)
+        uh.copy_(u)
+        torch.cuda.synchronize()
+        uh_np, yh_np = uh.numpy(), yh.numpy()
+        e_steps = max(2, min(args.steps, 5))
+        op.apply_host(uh_np, yh_np)                           # warm-up (allocates staging)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            op.apply_host(uh_np, yh_np)
+        torch.cuda.synchronize()
+        e_secs = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        e2e = {"value": ndofs_global * e_steps / (1e9 * e_secs), "unit": "GDoF/s",
+               "h2d_bytes_per_step": int(sum_over_ranks(mesh.ndofs_local * tsize)),
+               "d2h_bytes_per_step": int(sum_over_ranks(mesh.ndofs_local * tsize)),
+               "steps": e_steps, "ms_per_step": 1e3 * e_secs / e_steps,
+               "call": "bd_laplacian_apply_host (pinned host in/out vectors, synchronous)",
+               "y_norm_host": float(np.linalg.norm(yh_np[:mesh.ndofs_owned].astype(np.float64)))
+               if world == 1 else None}
+        del uh, yh
+
+    # ---- CPU baseline: the reference's CPU kernels on this box's host cores (rank 0, N = 1)
+    cpu = None
+    if world == 1 and rank == 0 and not args.no_cpu:
+        try:
+            g, cores, kind, sample, _, _ = cpu_reference_run(degree, args.float, 1000, 1, target_seconds=15.0)
+            cpu = {"value": g, "unit": "GDoF/s", "cores": cores, "kind": kind, "sample": sample}
+        except Exception as exc:  # the baseline is reported, never required for the GPU number
+            cpu = {"value": None, "unit": "GDoF/s", "cores": os.cpu_count(), "kind": "unavailable",
+                   "sample": f"{type(exc).__name__}: {exc}"}
+
+    if rank == 0:
+        line = {
+            "metric": "gdof_per_second_laplacian_action", "value": value, "unit": "GDoF/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic",
+            "config": dict(workload_config(args, world), mesh_cells=n, ndofs_global=ndofs_global,
+                           ncells_global=mesh.ncells_global, setup_seconds=t_setup),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cg": cg,
+            "gpu_launches": gpu_launches, "clocks": clocks,
+            "u_norm": unorm, "y_norm": ynorm,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -356,10 +356,21 @@ class MatFreeLaplacianGPU:
                                           _stream_ptr(stream)))
 
     def apply_host(self, in_host: np.ndarray, out_host: np.ndarray):
-        """Host-buffer entry point: H2D, apply, D2H (single rank)."""
+        """Host-buffer entry point: H2D, (forward scatter +) apply, D2H; synchronous."""
         assert in_host.dtype == self.value_type and out_host.dtype == self.value_type
         assert in_host.size == self.ndofs and out_host.size == self.ndofs
-        check(lib.bd_laplacian_apply_host(self._h, _ptr(in_host), _ptr(out_host)))
+        halo = self.halo._h if self.halo is not None else None
+        check(lib.bd_laplacian_apply_host(self._h, halo, _ptr(in_host), _ptr(out_host)))
+
+    def profile(self, enable: bool):
+        """Bracket every stiffness-kernel launch with CUDA events (roofline measurement)."""
+        check(lib.bd_laplacian_profile(self._h, int(enable)))
+
+    def profile_read(self):
+        """(summed kernel milliseconds, launches) since the last read."""
+        ms, n = C.c_double(), C.c_int64()
+        check(lib.bd_laplacian_profile_read(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def geometry(self) -> np.ndarray:
         """Host copy of the precomputed G, [n_lcells + n_bcells][6][nq^3]."""

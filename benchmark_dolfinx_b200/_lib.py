@@ -74,7 +74,9 @@ PROTOTYPES = {
     "bd_laplacian_destroy": (C.c_int, [_V]),
     "bd_laplacian_apply": (C.c_int, [_V, _V, _V, _V]),
     "bd_laplacian_apply_part": (C.c_int, [_V, C.c_int, _V, _V, _V]),
-    "bd_laplacian_apply_host": (C.c_int, [_V, _V, _V]),
+    "bd_laplacian_apply_host": (C.c_int, [_V, _V, _V, _V]),
+    "bd_laplacian_profile": (C.c_int, [_V, C.c_int]),
+    "bd_laplacian_profile_read": (C.c_int, [_V, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "bd_laplacian_geometry": (C.c_int, [_V, C.POINTER(_V), C.POINTER(C.c_int64)]),
     "bd_geometry_compute": (C.c_int, [C.c_int, C.c_int, _V, _V, _V, _V, _V, C.c_int64, _V, _V]),
     "bd_stiffness_apply": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _V, _V, _V, _V, _V, _V, _V,

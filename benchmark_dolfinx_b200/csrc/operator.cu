@@ -131,6 +131,9 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
 
 extern "C" int bd_laplacian_destroy(bd_laplacian* op)
 {
+  if (op)
+    for (cudaEvent_t e : op->prof_events)
+      cudaEventDestroy(e);
   delete op;
   return BD_SUCCESS;
 }
@@ -175,7 +178,48 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
     a.cells = op->cell_list.ptr + op->n_lcells;
     a.ncells = op->n_bcells;
   }
-  return stiffness_dispatch(op->scalar_bits, op->degree, op->nq, op->is_identity, a);
+  if (!op->profile || a.ncells == 0)
+    return stiffness_dispatch(op->scalar_bits, op->degree, op->nq, op->is_identity, a);
+  // bracket exactly the kernel launch with events on the launching stream
+  if (op->prof_used + 2 > op->prof_events.size())
+  {
+    for (int i = 0; i < 2; ++i)
+    {
+      cudaEvent_t e;
+      BD_CUDA_CHECK(cudaEventCreate(&e));
+      op->prof_events.push_back(e);
+    }
+  }
+  BD_CUDA_CHECK(cudaEventRecord(op->prof_events[op->prof_used], a.stream));
+  const int rc = stiffness_dispatch(op->scalar_bits, op->degree, op->nq, op->is_identity, a);
+  BD_CUDA_CHECK(cudaEventRecord(op->prof_events[op->prof_used + 1], a.stream));
+  op->prof_used += 2;
+  return rc;
+}
+
+extern "C" int bd_laplacian_profile(bd_laplacian* op, int enable)
+{
+  BD_REQUIRE(op, "bd_laplacian_profile: null operator");
+  op->profile = enable != 0;
+  op->prof_used = 0;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_laplacian_profile_read(bd_laplacian* op, double* total_ms, int64_t* launches)
+{
+  BD_REQUIRE(op && total_ms && launches, "bd_laplacian_profile_read: null argument");
+  double tot = 0;
+  for (size_t i = 0; i + 1 < op->prof_used; i += 2)
+  {
+    BD_CUDA_CHECK(cudaEventSynchronize(op->prof_events[i + 1]));
+    float ms = 0;
+    BD_CUDA_CHECK(cudaEventElapsedTime(&ms, op->prof_events[i], op->prof_events[i + 1]));
+    tot += ms;
+  }
+  *total_ms = tot;
+  *launches = static_cast<int64_t>(op->prof_used / 2);
+  op->prof_used = 0;
+  return BD_SUCCESS;
 }
 
 extern "C" int bd_laplacian_apply(bd_laplacian* op, const void* in_dev, void* out_dev, void* stream)
@@ -184,7 +228,8 @@ extern "C" int bd_laplacian_apply(bd_laplacian* op, const void* in_dev, void* ou
   return bd_laplacian_apply_part(op, 1, in_dev, out_dev, stream);
 }
 
-extern "C" int bd_laplacian_apply_host(bd_laplacian* op, const void* in_host, void* out_host)
+extern "C" int bd_laplacian_apply_host(bd_laplacian* op, bd_halo* halo, const void* in_host,
+                                       void* out_host)
 {
   BD_REQUIRE(op && in_host && out_host, "bd_laplacian_apply_host: null argument");
   const size_t bytes = static_cast<size_t>(op->ndofs) * op->scalar_size();
@@ -194,7 +239,7 @@ extern "C" int bd_laplacian_apply_host(bd_laplacian* op, const void* in_host, vo
     BD_CHECK(op->stage_out.alloc(bytes));
   }
   BD_CUDA_CHECK(cudaMemcpyAsync(op->stage_in.ptr, in_host, bytes, cudaMemcpyHostToDevice, nullptr));
-  BD_CHECK(bd_laplacian_apply(op, op->stage_in.ptr, op->stage_out.ptr, nullptr));
+  BD_CHECK(bd_laplacian_apply_halo(op, halo, op->stage_in.ptr, op->stage_out.ptr, nullptr));
   BD_CUDA_CHECK(cudaMemcpyAsync(out_host, op->stage_out.ptr, bytes, cudaMemcpyDeviceToHost, nullptr));
   BD_CUDA_CHECK(cudaStreamSynchronize(nullptr));
   return BD_SUCCESS;

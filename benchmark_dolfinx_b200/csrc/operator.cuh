@@ -21,6 +21,10 @@ struct bd_laplacian
   std::vector<char> phi0, dphi1;
   // staging for bd_laplacian_apply_host
   bd::DeviceArray<char> stage_in, stage_out;
+  // optional per-launch timing of the stiffness kernels (bd_laplacian_profile)
+  bool profile = false;
+  std::vector<cudaEvent_t> prof_events; // pairs (start, stop), consumed by bd_laplacian_profile_read
+  size_t prof_used = 0;
   // work vectors + scalars of bd_cg_solve, kept between calls
   bd::DeviceArray<char> cg_work;
   size_t scalar_size() const { return static_cast<size_t>(scalar_bits / 8); }

@@ -96,10 +96,21 @@ int bd_laplacian_apply(bd_laplacian* op, const void* in_dev, void* out_dev, void
 int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* in_dev, void* out_dev,
                             void* stream);
 
-/* End-to-end convenience for host vectors: H2D copy of `in_host`, apply, D2H copy
- * of the result, synchronous.  (The reference benchmark does the H2D at
- * src/laplacian_solver.cpp:108-109 and reads norms back at :130-131.) */
-int bd_laplacian_apply_host(bd_laplacian* op, const void* in_host, void* out_host);
+/* End-to-end entry point for HOST vectors of length ndofs: H2D copy of `in_host`, forward
+ * scatter (if `halo` is not NULL) + apply, D2H copy of the result, synchronous.  Pinned host
+ * memory gives full PCIe rate.  (The reference benchmark does the H2D at
+ * src/laplacian_solver.cpp:108-109 and reads results back at :130-131.) */
+struct bd_halo;
+int bd_laplacian_apply_host(bd_laplacian* op, struct bd_halo* halo, const void* in_host,
+                            void* out_host);
+
+/* Per-launch device timing of the stiffness kernels, for the roofline report: while enabled,
+ * every kernel launch of bd_laplacian_apply* is bracketed by CUDA events on the launching stream
+ * (no synchronisation); bd_laplacian_profile_read waits for them, returns the summed kernel time
+ * and the number of launches since the last read, and resets the counters.  (The reference only
+ * has dolfinx::common::Timer scopes around whole phases, src/laplacian_solver.cpp:90,197.) */
+int bd_laplacian_profile(bd_laplacian* op, int enable);
+int bd_laplacian_profile_read(bd_laplacian* op, double* total_ms, int64_t* launches);
 
 /* Read-only access to the precomputed geometry tensor, device pointer to
  * T [n_lcells + n_bcells][6][nq^3] (_g_entity, src/laplacian.hpp:429). */
