@@ -79,7 +79,8 @@ int cg_impl(bd_laplacian* op, bd_halo* halo, bd_comm* comm, T* x, const T* b, in
 {
   const std::int64_t ntot = op->ndofs;
   const std::int64_t n = halo ? halo->n_owned : ntot;
-  const size_t vbytes = static_cast<size_t>(ntot) * sizeof(T);
+  // each work vector starts on a 256-byte boundary (the doubles behind them need 8)
+  const size_t vbytes = (static_cast<size_t>(ntot) * sizeof(T) + 255) / 256 * 256;
   // workspace: r, y, p (the reference allocates them inside cg_solve, src/cg.hpp:103-105),
   // per-CTA partials and the device scalars
   const size_t need = 3 * vbytes + bd_dot_scratch_bytes() + 8 * sizeof(double);

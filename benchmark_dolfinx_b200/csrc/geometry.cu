@@ -11,16 +11,20 @@
 // write-bandwidth bound (48 B or 24 B per point out, the 8 vertices of a cell are shared by
 // its nq^3 threads through L1).
 #include "common.cuh"
+#include "stiffness_slab.cuh"
 
 namespace bd
 {
-template <typename T>
+// SLAB = false: the reference's layout G[c][6][nq^3];  SLAB = true: the batch-interleaved
+// layout the slab stiffness kernel streams (see stiffness_slab.cuh).
+template <typename T, bool SLAB>
 __global__ void __launch_bounds__(256)
     geometry_kernel(const T* __restrict__ xgeom, T* __restrict__ G,
                     const std::int32_t* __restrict__ geometry_dofmap, const T* __restrict__ dphi,
                     const T* __restrict__ weights, const std::int32_t* __restrict__ cells,
-                    std::int64_t ncells, int nq3)
+                    std::int64_t ncells, int nq)
 {
+  const int nq3 = nq * nq * nq;
   const std::int64_t total = ncells * nq3;
   const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
   for (std::int64_t idx = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -56,29 +60,81 @@ __global__ void __launch_bounds__(256)
     const T K22 = J[0][0] * J[1][1] - J[0][1] * J[1][0];
     const T detJ = J[0][0] * K00 - J[0][1] * K10 + J[0][2] * K20;
     const T w = __ldg(weights + q);
-    T* g = G + c * (6 * static_cast<std::int64_t>(nq3)) + q;
-    g[0] = (K00 * K00 + K01 * K01 + K02 * K02) * w / detJ;
-    g[nq3] = (K10 * K00 + K11 * K01 + K12 * K02) * w / detJ;
-    g[2 * nq3] = (K20 * K00 + K21 * K01 + K22 * K02) * w / detJ;
-    g[3 * nq3] = (K10 * K10 + K11 * K11 + K12 * K12) * w / detJ;
-    g[4 * nq3] = (K20 * K10 + K21 * K11 + K22 * K12) * w / detJ;
-    g[5 * nq3] = (K20 * K20 + K21 * K21 + K22 * K22) * w / detJ;
+    const T g0 = (K00 * K00 + K01 * K01 + K02 * K02) * w / detJ;
+    const T g1 = (K10 * K00 + K11 * K01 + K12 * K02) * w / detJ;
+    const T g2 = (K20 * K00 + K21 * K01 + K22 * K02) * w / detJ;
+    const T g3 = (K10 * K10 + K11 * K11 + K12 * K12) * w / detJ;
+    const T g4 = (K20 * K10 + K21 * K11 + K22 * K12) * w / detJ;
+    const T g5 = (K20 * K20 + K21 * K21 + K22 * K22) * w / detJ;
+    if constexpr (SLAB)
+    {
+      const int q0 = q / (nq * nq), q1 = (q / nq) % nq, q2 = q % nq;
+      const int row = (32 / nq) * nq;
+      T* g = G + slab_g_index(nq, c, 0, q0, q1, q2);
+      g[0] = g0;
+      g[row] = g1;
+      g[2 * row] = g2;
+      g[3 * row] = g3;
+      g[4 * row] = g4;
+      g[5 * row] = g5;
+    }
+    else
+    {
+      T* g = G + c * (6 * static_cast<std::int64_t>(nq3)) + q;
+      g[0] = g0;
+      g[nq3] = g1;
+      g[2 * nq3] = g2;
+      g[3 * nq3] = g3;
+      g[4 * nq3] = g4;
+      g[5 * nq3] = g5;
+    }
   }
 }
 
 template <typename T>
 int launch_geometry(int nq, const void* xgeom, const std::int32_t* gdofmap, const void* dphi,
                     const void* weights, const std::int32_t* cells, std::int64_t ncells, void* G,
-                    cudaStream_t stream)
+                    cudaStream_t stream, bool slab)
 {
   const int nq3 = nq * nq * nq;
   const std::int64_t total = ncells * nq3;
   const std::int64_t want = (total + 255) / 256;
   const std::int64_t cap = static_cast<std::int64_t>(sm_count()) * 8;
   const int grid = static_cast<int>(want < cap ? want : cap);
-  geometry_kernel<T><<<grid, 256, 0, stream>>>(static_cast<const T*>(xgeom), static_cast<T*>(G),
-                                               gdofmap, static_cast<const T*>(dphi),
-                                               static_cast<const T*>(weights), cells, ncells, nq3);
+  if (slab)
+    geometry_kernel<T, true><<<grid, 256, 0, stream>>>(static_cast<const T*>(xgeom), static_cast<T*>(G),
+                                                       gdofmap, static_cast<const T*>(dphi),
+                                                       static_cast<const T*>(weights), cells, ncells, nq);
+  else
+    geometry_kernel<T, false><<<grid, 256, 0, stream>>>(static_cast<const T*>(xgeom), static_cast<T*>(G),
+                                                        gdofmap, static_cast<const T*>(dphi),
+                                                        static_cast<const T*>(weights), cells, ncells, nq);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+int geometry_compute_slab(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
+                          const void* dphi, const void* weights, const std::int32_t* cells,
+                          std::int64_t ncells, void* G, cudaStream_t stream)
+{
+  if (ncells == 0)
+    return BD_SUCCESS;
+  return scalar_bits == 64
+             ? launch_geometry<double>(nq, xgeom, gdofmap, dphi, weights, cells, ncells, G, stream, true)
+             : launch_geometry<float>(nq, xgeom, gdofmap, dphi, weights, cells, ncells, G, stream, true);
+}
+
+int slab_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
+                        cudaStream_t stream)
+{
+  if (ncells == 0)
+    return BD_SUCCESS;
+  const int grid = sm_count() * 8;
+  if (scalar_bits == 64)
+    slab_g_to_reference_kernel<double><<<grid, 256, 0, stream>>>(nq, static_cast<const double*>(Gs),
+                                                                static_cast<double*>(G), ncells);
+  else
+    slab_g_to_reference_kernel<float><<<grid, 256, 0, stream>>>(nq, static_cast<const float*>(Gs),
+                                                               static_cast<float*>(G), ncells);
   BD_CUDA_CHECK(cudaGetLastError());
   return BD_SUCCESS;
 }
@@ -99,7 +155,7 @@ extern "C" int bd_geometry_compute(int scalar_bits, int nq, const void* xgeom,
              "bd_geometry_compute: null pointer argument");
   return scalar_bits == 64
              ? bd::launch_geometry<double>(nq, xgeom, geometry_dofmap, dphi_geometry, weights, cells,
-                                           ncells, G_out, bd::as_stream(stream))
+                                           ncells, G_out, bd::as_stream(stream), false)
              : bd::launch_geometry<float>(nq, xgeom, geometry_dofmap, dphi_geometry, weights, cells,
-                                          ncells, G_out, bd::as_stream(stream));
+                                          ncells, G_out, bd::as_stream(stream), false);
 }

@@ -116,11 +116,18 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
   TRY(copy_table(op->phi0, d->phi0, static_cast<size_t>(d->nq) * (d->degree + 1) * ts));
   TRY(copy_table(op->dphi1, d->dphi1, static_cast<size_t>(d->nq) * d->nq * ts));
   TRY(d->scalar_bits == 64 ? fill_constants<double>(op) : fill_constants<float>(op));
-  // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272)
-  TRY(op->G.alloc(static_cast<size_t>(nlist > 0 ? nlist : 1) * 6 * nq3 * ts));
-  TRY(bd_geometry_compute(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
-                          op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, nlist, op->G.ptr,
-                          nullptr));
+  // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272), written
+  // straight into the layout the stiffness kernel streams; lcells and bcells are separate segments
+  // because they are separate launches (the bcells pointer offset of src/laplacian.hpp:329).
+  op->g_bcells_offset = slab_g_size(op->nq, op->n_lcells);
+  const std::int64_t g_total = op->g_bcells_offset + slab_g_size(op->nq, op->n_bcells);
+  TRY(op->G.alloc(static_cast<size_t>(g_total > 0 ? g_total : 1) * ts));
+  TRY(geometry_compute_slab(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                            op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, op->n_lcells,
+                            op->G.ptr, nullptr));
+  TRY(geometry_compute_slab(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                            op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr + op->n_lcells,
+                            op->n_bcells, op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts, nullptr));
   if (cudaDeviceSynchronize() != cudaSuccess) // device_synchronize()  (src/laplacian.hpp:224)
     return guard_fail(fail(BD_ERR_CUDA, "geometry precompute failed: %s",
                            cudaGetErrorString(cudaGetLastError())));
@@ -141,8 +148,22 @@ extern "C" int bd_laplacian_destroy(bd_laplacian* op)
 extern "C" int bd_laplacian_geometry(bd_laplacian* op, const void** G_dev, int64_t* n_entries)
 {
   BD_REQUIRE(op && G_dev && n_entries, "bd_laplacian_geometry: null argument");
-  *G_dev = op->G.ptr;
-  *n_entries = (op->n_lcells + op->n_bcells) * op->g_cell_stride();
+  const std::int64_t nlist = op->n_lcells + op->n_bcells;
+  const size_t ts = op->scalar_size();
+  const size_t bytes = static_cast<size_t>(nlist) * op->g_cell_stride() * ts;
+  if (op->G_reference.count != bytes || bytes == 0)
+  {
+    BD_CHECK(op->G_reference.alloc(bytes > 0 ? bytes : 1));
+    BD_CHECK(slab_g_to_reference(op->scalar_bits, op->nq, op->G.ptr, op->G_reference.ptr, op->n_lcells,
+                                 nullptr));
+    BD_CHECK(slab_g_to_reference(op->scalar_bits, op->nq,
+                                 op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts,
+                                 op->G_reference.ptr + static_cast<size_t>(op->n_lcells) * op->g_cell_stride() * ts,
+                                 op->n_bcells, nullptr));
+    BD_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+  }
+  *G_dev = op->G_reference.ptr;
+  *n_entries = nlist * op->g_cell_stride();
   return BD_SUCCESS;
 }
 
@@ -161,6 +182,7 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
   a.phi0_host = op->phi0.data();
   a.dphi1_host = op->dphi1.data();
   a.stream = as_stream(stream);
+  a.slab = true;
   if (part == 0)
   {
     // set_value(out, 0) over owned + ghost entries (src/laplacian.hpp:359)
@@ -173,7 +195,7 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
   else
   {
     // geometry_ptr += 6 * Q^3 * lcells.size()  (src/laplacian.hpp:329)
-    a.G = op->G.ptr + static_cast<size_t>(op->n_lcells) * op->g_cell_stride() * ts;
+    a.G = op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts;
     a.cell_constants = op->cell_constants.ptr + static_cast<size_t>(op->n_lcells) * ts;
     a.cells = op->cell_list.ptr + op->n_lcells;
     a.ncells = op->n_bcells;

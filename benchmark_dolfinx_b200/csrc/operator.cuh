@@ -28,6 +28,10 @@ struct bd_laplacian
   // work vectors + scalars of bd_cg_solve, kept between calls
   bd::DeviceArray<char> cg_work;
   size_t scalar_size() const { return static_cast<size_t>(scalar_bits / 8); }
-  // offset (in entries of T) of the bcells part of G
+  // G is stored in the slab layout (stiffness_slab.cuh): lcells segment, then bcells segment,
+  // each rounded up to whole warp batches
+  bool slab = true;
+  std::int64_t g_bcells_offset = 0; // scalars before the bcells segment
+  bd::DeviceArray<char> G_reference; // reference-layout copy, built on demand (bd_laplacian_geometry)
   std::int64_t g_cell_stride() const { return 6ll * nq * nq * nq; }
 };

@@ -3,6 +3,7 @@
 
 #include "common.cuh"
 #include "stiffness.cuh"
+#include "stiffness_slab.cuh"
 
 namespace bd
 {
@@ -19,6 +20,7 @@ struct StiffnessArgs
   const void* phi0_host;  // T[nq*nd]
   const void* dphi1_host; // T[nq*nq]
   cudaStream_t stream;
+  bool slab = false; // G is in the slab layout (stiffness_slab.cuh) and the slab kernel is used
 };
 
 template <typename T, int P, int NQ, bool IDENTITY>
@@ -61,12 +63,72 @@ int launch_stiffness(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
+// The register-blocked kernel (stiffness_slab.cuh); `a.G` must be in the slab layout.
+template <typename T, int P, int NQ, bool IDENTITY>
+int launch_stiffness_slab(const StiffnessArgs& a)
+{
+  using C = SlabConfig<T, P, NQ>;
+  constexpr int ND = P + 1;
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  auto kernel = stiffness_slab_kernel<T, P, NQ, IDENTITY>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, C::THREADS, C::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  // Phi and DPhi = dphi1 * phi0 (products accumulated in double)
+  SlabTables<T, ND, NQ> tab;
+  const T* phi = static_cast<const T*>(a.phi0_host);
+  const T* dphi = static_cast<const T*>(a.dphi1_host);
+  for (int q = 0; q < NQ; ++q)
+    for (int i = 0; i < ND; ++i)
+    {
+      tab.phi[q * ND + i] = phi[q * ND + i];
+      if (IDENTITY)
+        tab.dphi[q * ND + i] = dphi[q * NQ + i];
+      else
+      {
+        double s = 0;
+        for (int r = 0; r < NQ; ++r)
+          s += static_cast<double>(dphi[q * NQ + r]) * static_cast<double>(phi[r * ND + i]);
+        tab.dphi[q * ND + i] = static_cast<T>(s);
+      }
+    }
+  const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
+  const std::int64_t want = (nbatches + C::WARPS - 1) / C::WARPS;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(want < max_grid ? want : max_grid);
+  kernel<<<grid, C::THREADS, C::CTA_SMEM, a.stream>>>(
+      static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
+      static_cast<const T*>(a.cell_constants), a.dofmap, a.cells, static_cast<int>(a.ncells), a.bc,
+      tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
 // One function per (scalar, qmode), each defined in its own translation unit so
 // the 28 kernel instantiations compile in parallel.
 int launch_stiffness_f64_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_f64_q1(int degree, const StiffnessArgs& a);
 int launch_stiffness_f32_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_f32_q1(int degree, const StiffnessArgs& a);
+
+// in geometry.cu
+int geometry_compute_slab(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
+                          const void* dphi, const void* weights, const std::int32_t* cells,
+                          std::int64_t ncells, void* G, cudaStream_t stream);
+int slab_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
+                        cudaStream_t stream);
 
 // Dispatch on (scalar_bits, degree, nq, identity); mirrors the reference's
 // dispatch and its error strings (src/laplacian.hpp:361-400).
