@@ -85,6 +85,7 @@ PROTOTYPES = {
     "bd_set_value": (C.c_int, [C.c_int, C.c_int64, C.c_double, _V, _V]),
     "bd_dot_scratch_bytes": (C.c_size_t, []),
     "bd_dot": (C.c_int, [C.c_int, C.c_int64, _V, _V, _V, _V, _V]),
+    "bd_dot_static": (C.c_int, [C.c_int, C.c_int64, _V, _V, _V, _V]),
     "bd_dot_host": (C.c_int, [C.c_int, C.c_int64, _V, _V, C.POINTER(C.c_double)]),
     "bd_pack": (C.c_int, [C.c_int, C.c_int64, _V, _V, _V, _V]),
     "bd_unpack": (C.c_int, [C.c_int, C.c_int64, _V, _V, _V, _V]),

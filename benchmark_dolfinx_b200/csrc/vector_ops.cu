@@ -5,6 +5,8 @@
 // second tiny kernel (bitwise reproducible, result stays in device memory).
 #include "vector_ops.cuh"
 
+#include <mutex>
+
 namespace bd
 {
 template <typename T>
@@ -211,4 +213,59 @@ extern "C" int bd_unpack(int scalar_bits, int64_t n, const int32_t* idx, const v
         n, idx, static_cast<const float*>(in), static_cast<float*>(out));
   BD_CUDA_CHECK(cudaGetLastError());
   return BD_SUCCESS;
+}
+
+// ---------------------------------------------------------------------------------------------
+// bd_dot_static: the same two-stage dot product, for callers that must not allocate.
+//
+// The per-CTA partial sums live in a file-scope device array instead of caller-provided scratch,
+// so the call needs no cudaMalloc (which would also synchronise the whole device in the middle
+// of an asynchronous solver loop) and works when the application has already committed all of the
+// GPU's memory.  Every GPU that loads the library holds these 16 KB until the process exits.
+// ---------------------------------------------------------------------------------------------
+namespace
+{
+static __device__ __align__(256) double g_static_dot_partials[bd::kMaxPartials];
+
+// In host code `g_static_dot_partials` is only a stand-in for the symbol, not a device address;
+// the address a kernel can use is looked up once per device, with that device current.
+std::mutex g_static_mutex;
+double* g_static_partials_of_device[64] = {nullptr};
+
+int static_partials(double** out)
+{
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return bd::fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (!g_static_partials_of_device[dev])
+  {
+    double* ptr = nullptr;
+    BD_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_static_dot_partials));
+    g_static_partials_of_device[dev] = ptr;
+  }
+  *out = g_static_partials_of_device[dev];
+  return BD_SUCCESS;
+}
+} // namespace
+
+extern "C" int bd_dot_static(int scalar_bits, int64_t n, const void* a, const void* b,
+                             double* result_dev, void* stream)
+{
+  BD_BITS_CHECK(scalar_bits);
+  BD_REQUIRE(n >= 0, "negative length");
+  if (n > BD_DOT_STATIC_MAX_N)
+    return fail(BD_ERR_INVALID_ARGUMENT,
+                "bd_dot_static: %lld entries exceed the supported maximum of %lld (use bd_dot with "
+                "caller-provided scratch for longer vectors)",
+                (long long)n, (long long)BD_DOT_STATIC_MAX_N);
+  BD_REQUIRE(result_dev, "bd_dot_static: null result pointer");
+  BD_REQUIRE(n == 0 || (a && b), "bd_dot_static: null vector pointer");
+  double* partials = nullptr;
+  BD_CHECK(static_partials(&partials));
+  // Nothing in the array has to start at zero: the first kernel overwrites partials[0, grid) and
+  // the second reads exactly those entries, so whatever the previous call left behind is ignored.
+  return scalar_bits == 64 ? dot_impl<double>(n, a, b, result_dev, partials, as_stream(stream))
+                           : dot_impl<float>(n, a, b, result_dev, partials, as_stream(stream));
 }

@@ -149,6 +149,26 @@ size_t bd_dot_scratch_bytes(void);
  * bd_dot_scratch_bytes() bytes and must not be shared by overlapping calls. */
 int bd_dot(int scalar_bits, int64_t n, const void* a, const void* b, double* result_dev,
            void* scratch_dev, void* stream);
+/* Allocation-free variant of bd_dot.  It has no counterpart in the reference (whose
+ * thrust::inner_product allocates its own temporary storage on every call).  It exists for host
+ * codes that cannot let a library allocate on the device: a solver loop kept fully asynchronous
+ * (cudaMalloc / cudaFree synchronise the device), or a run that has already handed all of the
+ * GPU's memory to its own pools, where a late cudaMalloc can simply fail.  The per-CTA partial
+ * sums go to a fixed 16 KB array in the library's device image (one copy on every GPU that loads
+ * the library, held until exit) instead of caller scratch; the call itself performs no
+ * cudaMalloc / cudaFree and calls no allocating routine.
+ *   - Vectors of up to BD_DOT_STATIC_MAX_N entries; longer ones are rejected with
+ *     BD_ERR_INVALID_ARGUMENT (use bd_dot).
+ *   - The first call on each device looks up the array's device address (that device must be
+ *     current); make that first call before starting any stream capture.
+ *   - All calls on a device share the array: two calls whose kernels can overlap on the GPU
+ *     (different streams, or different host threads) race on it and give wrong sums; calls on
+ *     one stream are safe.  The array keeps the previous call's partial sums; none of it needs
+ *     clearing, every entry that is read is first overwritten by the same call.
+ *   - Same kernels, grid and summation order as bd_dot: results are bitwise identical. */
+#define BD_DOT_STATIC_MAX_N 2147483647LL
+int bd_dot_static(int scalar_bits, int64_t n, const void* a, const void* b, double* result_dev,
+                  void* stream);
 /* Host-returning convenience: local dot, synchronous (allocates its own scratch). */
 int bd_dot_host(int scalar_bits, int64_t n, const void* a, const void* b, double* result_host);
 /* out[i] = in[idx[i]]   (pack_gpu, src/vector.hpp:31-41) */
