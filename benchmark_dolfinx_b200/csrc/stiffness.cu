@@ -1,8 +1,26 @@
 // Dispatch + C entry point for the stiffness kernel.
 #include "stiffness_launch.cuh"
 
+#include <cstdlib>
+#include <cstring>
+
 namespace bd
 {
+int stiffness_variant()
+{
+  static const int v = [] {
+    const char* e = std::getenv("BD_STIFFNESS_VARIANT");
+    if (!e)
+      return 0;
+    if (!std::strcmp(e, "slab"))
+      return 1;
+    if (!std::strcmp(e, "tma"))
+      return 2;
+    return 0;
+  }();
+  return v;
+}
+
 int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const StiffnessArgs& a)
 {
   if (scalar_bits != 32 && scalar_bits != 64)

@@ -7,6 +7,9 @@
 
 namespace bd
 {
+// 0 = default choice, 1 = plain slab kernel, 2 = asynchronous-copy slab kernel (env BD_STIFFNESS_VARIANT)
+int stiffness_variant();
+
 struct StiffnessArgs
 {
   const void* u;
@@ -63,12 +66,82 @@ int launch_stiffness(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
+template <typename T, int ND, int NQ, bool IDENTITY>
+void fill_slab_tables(SlabTables<T, ND, NQ>& tab, const void* phi0_host, const void* dphi1_host)
+{
+  // Phi and DPhi = dphi1 * phi0 (products accumulated in double)
+  const T* phi = static_cast<const T*>(phi0_host);
+  const T* dphi = static_cast<const T*>(dphi1_host);
+  for (int q = 0; q < NQ; ++q)
+    for (int i = 0; i < ND; ++i)
+    {
+      tab.phi[q * ND + i] = phi[q * ND + i];
+      if (IDENTITY)
+        tab.dphi[q * ND + i] = dphi[q * NQ + i];
+      else
+      {
+        double s = 0;
+        for (int r = 0; r < NQ; ++r)
+          s += static_cast<double>(dphi[q * NQ + r]) * static_cast<double>(phi[r * ND + i]);
+        tab.dphi[q * ND + i] = static_cast<T>(s);
+      }
+    }
+}
+
+// Slab kernel with the G stream on asynchronous bulk copies (stiffness_slab.cuh).
+template <typename T, int P, int NQ, bool IDENTITY, int NSTAGE>
+int launch_stiffness_slab_tma(const StiffnessArgs& a)
+{
+  using C = SlabConfig<T, P, NQ>;
+  using TC = SlabTmaConfig<T, P, NQ, NSTAGE>;
+  constexpr int ND = P + 1;
+  if constexpr (!TC::SUPPORTED)
+    return fail(BD_ERR_UNSUPPORTED, "asynchronous-copy slab kernel unsupported for this configuration");
+  else
+  {
+    auto kernel = stiffness_slab_tma_kernel<T, P, NQ, IDENTITY, NSTAGE>;
+    static thread_local int blocks_per_sm[64] = {0};
+    int dev = 0;
+    BD_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64)
+      return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+    if (blocks_per_sm[dev] == 0)
+    {
+      BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC::CTA_SMEM));
+      int nb = 0;
+      BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, TC::THREADS, TC::CTA_SMEM));
+      blocks_per_sm[dev] = nb > 0 ? nb : 1;
+    }
+    SlabTables<T, ND, NQ> tab;
+    fill_slab_tables<T, ND, NQ, IDENTITY>(tab, a.phi0_host, a.dphi1_host);
+    const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
+    const std::int64_t want = (nbatches + TC::WARPS - 1) / TC::WARPS;
+    const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+    const int grid = static_cast<int>(want < max_grid ? want : max_grid);
+    kernel<<<grid, TC::THREADS, TC::CTA_SMEM, a.stream>>>(
+        static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
+        static_cast<const T*>(a.cell_constants), a.dofmap, a.cells, static_cast<int>(a.ncells), a.bc, tab);
+    BD_CUDA_CHECK(cudaGetLastError());
+    return BD_SUCCESS;
+  }
+}
+
 // The register-blocked kernel (stiffness_slab.cuh); `a.G` must be in the slab layout.
 template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_slab(const StiffnessArgs& a)
 {
   using C = SlabConfig<T, P, NQ>;
   constexpr int ND = P + 1;
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  // kernel selection (BD_STIFFNESS_VARIANT=slab|tma overrides; measured choices in DESIGN.md)
+  if constexpr (NQ <= 5 && SlabTmaConfig<T, P, NQ, 3>::SUPPORTED)
+  {
+    if (stiffness_variant() != 1)
+      return launch_stiffness_slab_tma<T, P, NQ, IDENTITY, 3>(a);
+  }
   if (a.ncells == 0)
     return BD_SUCCESS;
   if (a.ncells > 0x7fffffffLL)
@@ -86,24 +159,8 @@ int launch_stiffness_slab(const StiffnessArgs& a)
     BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, C::THREADS, C::CTA_SMEM));
     blocks_per_sm[dev] = nb > 0 ? nb : 1;
   }
-  // Phi and DPhi = dphi1 * phi0 (products accumulated in double)
   SlabTables<T, ND, NQ> tab;
-  const T* phi = static_cast<const T*>(a.phi0_host);
-  const T* dphi = static_cast<const T*>(a.dphi1_host);
-  for (int q = 0; q < NQ; ++q)
-    for (int i = 0; i < ND; ++i)
-    {
-      tab.phi[q * ND + i] = phi[q * ND + i];
-      if (IDENTITY)
-        tab.dphi[q * ND + i] = dphi[q * NQ + i];
-      else
-      {
-        double s = 0;
-        for (int r = 0; r < NQ; ++r)
-          s += static_cast<double>(dphi[q * NQ + r]) * static_cast<double>(phi[r * ND + i]);
-        tab.dphi[q * ND + i] = static_cast<T>(s);
-      }
-    }
+  fill_slab_tables<T, ND, NQ, IDENTITY>(tab, a.phi0_host, a.dphi1_host);
   const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
   const std::int64_t want = (nbatches + C::WARPS - 1) / C::WARPS;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
