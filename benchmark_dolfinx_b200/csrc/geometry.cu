@@ -11,13 +11,15 @@
 // write-bandwidth bound (48 B or 24 B per point out, the 8 vertices of a cell are shared by
 // its nq^3 threads through L1).
 #include "common.cuh"
+#include "stiffness_mma8.cuh"
 #include "stiffness_slab.cuh"
 
 namespace bd
 {
-// SLAB = false: the reference's layout G[c][6][nq^3];  SLAB = true: the batch-interleaved
-// layout the slab stiffness kernel streams (see stiffness_slab.cuh).
-template <typename T, bool SLAB>
+// LAYOUT 0: the reference's layout G[c][6][nq^3];  1: the batch-interleaved layout the slab
+// stiffness kernel streams (stiffness_slab.cuh);  2: accumulator order for the DMMA kernel
+// (stiffness_mma8.cuh, nq = 8).
+template <typename T, int LAYOUT>
 __global__ void __launch_bounds__(256)
     geometry_kernel(const T* __restrict__ xgeom, T* __restrict__ G,
                     const std::int32_t* __restrict__ geometry_dofmap, const T* __restrict__ dphi,
@@ -66,7 +68,18 @@ __global__ void __launch_bounds__(256)
     const T g3 = (K10 * K10 + K11 * K11 + K12 * K12) * w / detJ;
     const T g4 = (K20 * K10 + K21 * K11 + K22 * K12) * w / detJ;
     const T g5 = (K20 * K20 + K21 * K21 + K22 * K22) * w / detJ;
-    if constexpr (SLAB)
+    if constexpr (LAYOUT == 2)
+    {
+      const int q0 = q / (nq * nq), q1 = (q / nq) % nq, q2 = q % nq;
+      T* g = G + mma8_g_index(c, 0, q0, q1, q2);
+      g[0] = g0;
+      g[64] = g1;
+      g[128] = g2;
+      g[192] = g3;
+      g[256] = g4;
+      g[320] = g5;
+    }
+    else if constexpr (LAYOUT == 1)
     {
       const int q0 = q / (nq * nq), q1 = (q / nq) % nq, q2 = q % nq;
       const int row = (32 / nq) * nq;
@@ -94,41 +107,67 @@ __global__ void __launch_bounds__(256)
 template <typename T>
 int launch_geometry(int nq, const void* xgeom, const std::int32_t* gdofmap, const void* dphi,
                     const void* weights, const std::int32_t* cells, std::int64_t ncells, void* G,
-                    cudaStream_t stream, bool slab)
+                    cudaStream_t stream, int layout)
 {
   const int nq3 = nq * nq * nq;
   const std::int64_t total = ncells * nq3;
   const std::int64_t want = (total + 255) / 256;
   const std::int64_t cap = static_cast<std::int64_t>(sm_count()) * 8;
   const int grid = static_cast<int>(want < cap ? want : cap);
-  if (slab)
-    geometry_kernel<T, true><<<grid, 256, 0, stream>>>(static_cast<const T*>(xgeom), static_cast<T*>(G),
-                                                       gdofmap, static_cast<const T*>(dphi),
-                                                       static_cast<const T*>(weights), cells, ncells, nq);
+#define BD_GEOM_LAUNCH(L)                                                                          \
+  geometry_kernel<T, L><<<grid, 256, 0, stream>>>(static_cast<const T*>(xgeom), static_cast<T*>(G),     \
+                                                  gdofmap, static_cast<const T*>(dphi),                \
+                                                  static_cast<const T*>(weights), cells, ncells, nq)
+  if (layout == 2)
+    BD_GEOM_LAUNCH(2);
+  else if (layout == 1)
+    BD_GEOM_LAUNCH(1);
   else
-    geometry_kernel<T, false><<<grid, 256, 0, stream>>>(static_cast<const T*>(xgeom), static_cast<T*>(G),
-                                                        gdofmap, static_cast<const T*>(dphi),
-                                                        static_cast<const T*>(weights), cells, ncells, nq);
+    BD_GEOM_LAUNCH(0);
+#undef BD_GEOM_LAUNCH
   BD_CUDA_CHECK(cudaGetLastError());
   return BD_SUCCESS;
 }
-int geometry_compute_slab(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
-                          const void* dphi, const void* weights, const std::int32_t* cells,
-                          std::int64_t ncells, void* G, cudaStream_t stream)
+
+int geometry_compute_layout(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
+                            const void* dphi, const void* weights, const std::int32_t* cells,
+                            std::int64_t ncells, void* G, cudaStream_t stream, int layout)
 {
   if (ncells == 0)
     return BD_SUCCESS;
   return scalar_bits == 64
-             ? launch_geometry<double>(nq, xgeom, gdofmap, dphi, weights, cells, ncells, G, stream, true)
-             : launch_geometry<float>(nq, xgeom, gdofmap, dphi, weights, cells, ncells, G, stream, true);
+             ? launch_geometry<double>(nq, xgeom, gdofmap, dphi, weights, cells, ncells, G, stream, layout)
+             : launch_geometry<float>(nq, xgeom, gdofmap, dphi, weights, cells, ncells, G, stream, layout);
 }
 
-int slab_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
-                        cudaStream_t stream)
+__global__ void __launch_bounds__(256)
+    mma8_g_to_reference_kernel(const double* __restrict__ Gf, double* __restrict__ G, std::int64_t ncells)
+{
+  const std::int64_t total = ncells * 6 * 512;
+  const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
+  for (std::int64_t idx = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+       idx += stride)
+  {
+    const std::int64_t pos = idx / 3072;
+    const int rem = static_cast<int>(idx - pos * 3072);
+    const int comp = rem / 512, q = rem % 512;
+    G[idx] = Gf[mma8_g_index(pos, comp, q / 64, (q / 8) % 8, q % 8)];
+  }
+}
+
+int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
+                          cudaStream_t stream, int layout)
 {
   if (ncells == 0)
     return BD_SUCCESS;
   const int grid = sm_count() * 8;
+  if (layout == 2)
+  {
+    mma8_g_to_reference_kernel<<<grid, 256, 0, stream>>>(static_cast<const double*>(Gs),
+                                                         static_cast<double*>(G), ncells);
+    BD_CUDA_CHECK(cudaGetLastError());
+    return BD_SUCCESS;
+  }
   if (scalar_bits == 64)
     slab_g_to_reference_kernel<double><<<grid, 256, 0, stream>>>(nq, static_cast<const double*>(Gs),
                                                                 static_cast<double*>(G), ncells);
@@ -155,7 +194,7 @@ extern "C" int bd_geometry_compute(int scalar_bits, int nq, const void* xgeom,
              "bd_geometry_compute: null pointer argument");
   return scalar_bits == 64
              ? bd::launch_geometry<double>(nq, xgeom, geometry_dofmap, dphi_geometry, weights, cells,
-                                           ncells, G_out, bd::as_stream(stream), false)
+                                           ncells, G_out, bd::as_stream(stream), 0)
              : bd::launch_geometry<float>(nq, xgeom, geometry_dofmap, dphi_geometry, weights, cells,
-                                          ncells, G_out, bd::as_stream(stream), false);
+                                          ncells, G_out, bd::as_stream(stream), 0);
 }

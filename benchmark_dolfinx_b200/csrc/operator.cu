@@ -116,18 +116,23 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
   TRY(copy_table(op->phi0, d->phi0, static_cast<size_t>(d->nq) * (d->degree + 1) * ts));
   TRY(copy_table(op->dphi1, d->dphi1, static_cast<size_t>(d->nq) * d->nq * ts));
   TRY(d->scalar_bits == 64 ? fill_constants<double>(op) : fill_constants<float>(op));
+  TRY(op->masked_dofmap.alloc(static_cast<size_t>(d->ncells * nd3 > 0 ? d->ncells * nd3 : 1)));
+  TRY(build_masked_dofmap(d->ncells * nd3, op->cell_dofmap.ptr, op->bc_marker.ptr, op->masked_dofmap.ptr,
+                          nullptr));
   // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272), written
   // straight into the layout the stiffness kernel streams; lcells and bcells are separate segments
   // because they are separate launches (the bcells pointer offset of src/laplacian.hpp:329).
-  op->g_bcells_offset = slab_g_size(op->nq, op->n_lcells);
-  const std::int64_t g_total = op->g_bcells_offset + slab_g_size(op->nq, op->n_bcells);
+  op->g_layout = preferred_g_layout(op->scalar_bits, op->nq);
+  op->g_bcells_offset = g_layout_size(op->g_layout, op->nq, op->n_lcells);
+  const std::int64_t g_total = op->g_bcells_offset + g_layout_size(op->g_layout, op->nq, op->n_bcells);
   TRY(op->G.alloc(static_cast<size_t>(g_total > 0 ? g_total : 1) * ts));
-  TRY(geometry_compute_slab(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
-                            op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, op->n_lcells,
-                            op->G.ptr, nullptr));
-  TRY(geometry_compute_slab(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
-                            op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr + op->n_lcells,
-                            op->n_bcells, op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts, nullptr));
+  TRY(geometry_compute_layout(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                              op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, op->n_lcells,
+                              op->G.ptr, nullptr, op->g_layout));
+  TRY(geometry_compute_layout(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                              op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr + op->n_lcells,
+                              op->n_bcells, op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts, nullptr,
+                              op->g_layout));
   if (cudaDeviceSynchronize() != cudaSuccess) // device_synchronize()  (src/laplacian.hpp:224)
     return guard_fail(fail(BD_ERR_CUDA, "geometry precompute failed: %s",
                            cudaGetErrorString(cudaGetLastError())));
@@ -154,12 +159,12 @@ extern "C" int bd_laplacian_geometry(bd_laplacian* op, const void** G_dev, int64
   if (op->G_reference.count != bytes || bytes == 0)
   {
     BD_CHECK(op->G_reference.alloc(bytes > 0 ? bytes : 1));
-    BD_CHECK(slab_g_to_reference(op->scalar_bits, op->nq, op->G.ptr, op->G_reference.ptr, op->n_lcells,
-                                 nullptr));
-    BD_CHECK(slab_g_to_reference(op->scalar_bits, op->nq,
-                                 op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts,
-                                 op->G_reference.ptr + static_cast<size_t>(op->n_lcells) * op->g_cell_stride() * ts,
-                                 op->n_bcells, nullptr));
+    BD_CHECK(layout_g_to_reference(op->scalar_bits, op->nq, op->G.ptr, op->G_reference.ptr, op->n_lcells,
+                                   nullptr, op->g_layout));
+    BD_CHECK(layout_g_to_reference(op->scalar_bits, op->nq,
+                                   op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts,
+                                   op->G_reference.ptr + static_cast<size_t>(op->n_lcells) * op->g_cell_stride() * ts,
+                                   op->n_bcells, nullptr, op->g_layout));
     BD_CUDA_CHECK(cudaStreamSynchronize(nullptr));
   }
   *G_dev = op->G_reference.ptr;
@@ -183,6 +188,8 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
   a.dphi1_host = op->dphi1.data();
   a.stream = as_stream(stream);
   a.slab = true;
+  a.g_layout = op->g_layout;
+  a.mdofmap = op->masked_dofmap.ptr;
   if (part == 0)
   {
     // set_value(out, 0) over owned + ghost entries (src/laplacian.hpp:359)

@@ -16,6 +16,7 @@ struct bd_laplacian
   // device data (owned or borrowed)
   bd::DeviceArray<std::int32_t> cell_dofmap, geometry_dofmap, cell_list; // cell_list = [lcells.., bcells..]
   bd::DeviceArray<std::int8_t> bc_marker;
+  bd::DeviceArray<std::int32_t> masked_dofmap; // cell_dofmap with the BC marker in bit 31
   bd::DeviceArray<char> xgeom, weights, dphi_geometry, G, cell_constants;
   // 1-D tables on the host (they travel to the kernel as a launch parameter)
   std::vector<char> phi0, dphi1;
@@ -31,6 +32,7 @@ struct bd_laplacian
   // G is stored in the slab layout (stiffness_slab.cuh): lcells segment, then bcells segment,
   // each rounded up to whole warp batches
   bool slab = true;
+  int g_layout = 1; // 1 slab, 2 DMMA accumulator order (see stiffness_launch.cuh)
   std::int64_t g_bcells_offset = 0; // scalars before the bcells segment
   bd::DeviceArray<char> G_reference; // reference-layout copy, built on demand (bd_laplacian_geometry)
   std::int64_t g_cell_stride() const { return 6ll * nq * nq * nq; }

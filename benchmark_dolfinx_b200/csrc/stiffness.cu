@@ -21,8 +21,54 @@ int stiffness_variant()
   return v;
 }
 
+__global__ void __launch_bounds__(256)
+    mask_dofmap_kernel(std::int64_t n, const std::int32_t* __restrict__ dofmap,
+                       const std::int8_t* __restrict__ bc, std::int32_t* __restrict__ out)
+{
+  const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
+  for (std::int64_t i = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+  {
+    const std::int32_t d = dofmap[i];
+    out[i] = bc[d] ? (d | kBcBit) : d;
+  }
+}
+
+int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::int8_t* bc,
+                        std::int32_t* out, cudaStream_t stream)
+{
+  if (n == 0)
+    return BD_SUCCESS;
+  const std::int64_t want = (n + 1023) / 1024;
+  const std::int64_t cap = static_cast<std::int64_t>(sm_count()) * 8;
+  mask_dofmap_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, stream>>>(n, dofmap, bc, out);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+int preferred_g_layout(int scalar_bits, int nq)
+{
+  if (scalar_bits == 64 && nq == 8 && stiffness_variant() != 1)
+    return 2;
+  return 1;
+}
+
+std::int64_t g_layout_size(int layout, int nq, std::int64_t ncells)
+{
+  if (layout == 2)
+    return ncells * 3072;
+  if (layout == 1)
+    return slab_g_size(nq, ncells);
+  return ncells * 6 * nq * nq * nq;
+}
+
 int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const StiffnessArgs& a)
 {
+  if (a.g_layout == 2)
+  {
+    if (scalar_bits != 64 || nq != 8)
+      return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA layout needs fp64 and nq = 8");
+    return launch_stiffness_mma8(degree, identity, a);
+  }
   if (scalar_bits != 32 && scalar_bits != 64)
     return fail(BD_ERR_INVALID_ARGUMENT, "Invalid float size. Must be 32 or 64.");
   if (degree < 1 || degree > 7)

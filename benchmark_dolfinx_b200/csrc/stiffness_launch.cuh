@@ -23,7 +23,9 @@ struct StiffnessArgs
   const void* phi0_host;  // T[nq*nd]
   const void* dphi1_host; // T[nq*nq]
   cudaStream_t stream;
+  const std::int32_t* mdofmap = nullptr; // dofmap with the BC marker in bit 31 (asynchronous-copy kernel)
   bool slab = false; // G is in the slab layout (stiffness_slab.cuh) and the slab kernel is used
+  int g_layout = 0;  // 0 reference, 1 slab, 2 DMMA accumulator order
 };
 
 template <typename T, int P, int NQ, bool IDENTITY>
@@ -88,18 +90,33 @@ void fill_slab_tables(SlabTables<T, ND, NQ>& tab, const void* phi0_host, const v
     }
 }
 
+// Tuning of the asynchronous-copy kernel per 1-D quadrature size: ring depth, q0 rows per slot,
+// warps per CTA and whether the next batch's gather is prefetched into registers.
+template <int NQ>
+struct SlabTmaTuning
+{
+  static constexpr int NSTAGE = NQ <= 5 ? 3 : 4;
+  static constexpr int Q0C = NQ <= 5 ? NQ : (NQ == 6 ? 3 : (NQ == 8 ? 2 : (NQ == 9 ? 3 : NQ)));
+  static constexpr int WARPS = NQ <= 5 ? 2 : 1;
+  static constexpr bool PREFETCH = NQ <= 5;
+};
+
 // Slab kernel with the G stream on asynchronous bulk copies (stiffness_slab.cuh).
-template <typename T, int P, int NQ, bool IDENTITY, int NSTAGE>
+template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_slab_tma(const StiffnessArgs& a)
 {
   using C = SlabConfig<T, P, NQ>;
-  using TC = SlabTmaConfig<T, P, NQ, NSTAGE>;
+  using TU = SlabTmaTuning<NQ>;
+  constexpr int NSTAGE = (NQ == 7) ? 2 : TU::NSTAGE;
+  using TC = SlabTmaConfig<T, P, NQ, NSTAGE, TU::Q0C, TU::WARPS>;
   constexpr int ND = P + 1;
   if constexpr (!TC::SUPPORTED)
     return fail(BD_ERR_UNSUPPORTED, "asynchronous-copy slab kernel unsupported for this configuration");
   else
   {
-    auto kernel = stiffness_slab_tma_kernel<T, P, NQ, IDENTITY, NSTAGE>;
+    if (!a.mdofmap)
+      return fail(BD_ERR_INVALID_ARGUMENT, "the asynchronous-copy kernel needs the masked dofmap");
+    auto kernel = stiffness_slab_tma_kernel<T, P, NQ, IDENTITY, NSTAGE, TU::Q0C, TU::WARPS, TU::PREFETCH>;
     static thread_local int blocks_per_sm[64] = {0};
     int dev = 0;
     BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -120,10 +137,17 @@ int launch_stiffness_slab_tma(const StiffnessArgs& a)
     const int grid = static_cast<int>(want < max_grid ? want : max_grid);
     kernel<<<grid, TC::THREADS, TC::CTA_SMEM, a.stream>>>(
         static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
-        static_cast<const T*>(a.cell_constants), a.dofmap, a.cells, static_cast<int>(a.ncells), a.bc, tab);
+        static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
     BD_CUDA_CHECK(cudaGetLastError());
     return BD_SUCCESS;
   }
+}
+
+template <typename T, int P, int NQ>
+constexpr bool slab_tma_supported()
+{
+  using TU = SlabTmaTuning<NQ>;
+  return SlabTmaConfig<T, P, NQ, (NQ == 7) ? 2 : TU::NSTAGE, TU::Q0C, TU::WARPS>::SUPPORTED;
 }
 
 // The register-blocked kernel (stiffness_slab.cuh); `a.G` must be in the slab layout.
@@ -137,10 +161,10 @@ int launch_stiffness_slab(const StiffnessArgs& a)
   if (a.ncells > 0x7fffffffLL)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   // kernel selection (BD_STIFFNESS_VARIANT=slab|tma overrides; measured choices in DESIGN.md)
-  if constexpr (NQ <= 5 && SlabTmaConfig<T, P, NQ, 3>::SUPPORTED)
+  if constexpr (slab_tma_supported<T, P, NQ>())
   {
-    if (stiffness_variant() != 1)
-      return launch_stiffness_slab_tma<T, P, NQ, IDENTITY, 3>(a);
+    if (stiffness_variant() != 1 && a.mdofmap)
+      return launch_stiffness_slab_tma<T, P, NQ, IDENTITY>(a);
   }
   if (a.ncells == 0)
     return BD_SUCCESS;
@@ -181,11 +205,21 @@ int launch_stiffness_f32_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_f32_q1(int degree, const StiffnessArgs& a);
 
 // in geometry.cu
-int geometry_compute_slab(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
-                          const void* dphi, const void* weights, const std::int32_t* cells,
-                          std::int64_t ncells, void* G, cudaStream_t stream);
-int slab_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
-                        cudaStream_t stream);
+// G layouts: 0 = reference [cell][6][nq^3], 1 = slab (stiffness_slab.cuh), 2 = DMMA accumulator
+// order (stiffness_mma8.cuh; nq = 8, fp64 only)
+int geometry_compute_layout(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
+                            const void* dphi, const void* weights, const std::int32_t* cells,
+                            std::int64_t ncells, void* G, cudaStream_t stream, int layout);
+int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
+                          cudaStream_t stream, int layout);
+// Layout the operator should use for (scalar_bits, nq) and the scalars it needs for ncells cells.
+int preferred_g_layout(int scalar_bits, int nq);
+std::int64_t g_layout_size(int layout, int nq, std::int64_t ncells);
+// in stiffness_mma8.cu
+int launch_stiffness_mma8(int degree, bool identity, const StiffnessArgs& a);
+// in stiffness.cu: out[i] = dofmap[i] | (bc[dofmap[i]] ? 0x80000000 : 0)
+int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::int8_t* bc,
+                        std::int32_t* out, cudaStream_t stream);
 
 // Dispatch on (scalar_bits, degree, nq, identity); mirrors the reference's
 // dispatch and its error strings (src/laplacian.hpp:361-400).

@@ -1,0 +1,58 @@
+// Launcher of the fp64 tensor-core kernel (stiffness_mma8.cuh).
+#include "stiffness_launch.cuh"
+#include "stiffness_mma8.cuh"
+
+namespace bd
+{
+template <int P, bool IDENTITY>
+static int launch_mma8(const StiffnessArgs& a)
+{
+  constexpr int ND = P + 1;
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  if (!a.mdofmap)
+    return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA kernel needs the masked dofmap");
+  auto kernel = stiffness_mma8_kernel<P, IDENTITY>;
+  constexpr int smem = kMma8Warps * kMma8WarpSmem;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kMma8Warps * 32, smem));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  Mma8Tables tab{};
+  const double* phi = static_cast<const double*>(a.phi0_host);   // [8][ND]
+  const double* dphi = static_cast<const double*>(a.dphi1_host); // [8][8]
+  for (int q = 0; q < 8; ++q)
+    for (int i = 0; i < 8; ++i)
+    {
+      tab.phi[q * 8 + i] = i < ND ? phi[q * ND + i] : 0.0;
+      tab.dphi[q * 8 + i] = dphi[q * 8 + i];
+    }
+  const std::int64_t want = (a.ncells + kMma8Warps - 1) / kMma8Warps;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(want < max_grid ? want : max_grid);
+  kernel<<<grid, kMma8Warps * 32, smem, a.stream>>>(
+      static_cast<const double*>(a.u), static_cast<double*>(a.y), static_cast<const double*>(a.G),
+      static_cast<const double*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+int launch_stiffness_mma8(int degree, bool identity, const StiffnessArgs& a)
+{
+  if (degree == 6 && !identity)
+    return launch_mma8<6, false>(a);
+  if (degree == 7 && identity)
+    return launch_mma8<7, true>(a);
+  return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers degree 6 / qmode 1 and degree 7 / qmode 0 only");
+}
+} // namespace bd

@@ -1,0 +1,288 @@
+// fp64 tensor-core (DMMA) stiffness action for 8 quadrature points per direction
+// (degree 6 with qmode 1, degree 7 with qmode 0), sm_100a.
+//
+// Why: for nq = 8 the slab kernel is limited by per-thread state (49-64 values per dof plane ->
+// spills, 4 warps per SM) and reaches ~20 % of the HBM roofline (profiles/r1_v4_*), while the
+// contractions are compute-heavy (~50k FMA per cell).  On B200 mma.sync.m8n8k4.f64 runs at the full
+// fp64 rate (37 TFLOP/s measured, scripts/microbench/fp64_rates.cu) with 1/8 of the instructions
+// and no shared-memory operand traffic, and 8 x 8 x 8 maps onto it exactly.
+//
+// One warp owns one cell.  A cell tensor T[x][y][z] (8 x 8 x 8) lives in the warp's registers in
+// the layout of the MMA accumulator: lane = 4*x + t holds T[x][y][2t], T[x][y][2t+1] for y = 0..7
+// (16 doubles per lane).  With that single layout the three kinds of 1-D contraction are:
+//   z (column index):  the tile T[:, y, :] is directly a valid A operand -- its two accumulator
+//                      registers are the two k-steps when the constant B operand is permuted
+//                      accordingly -- so D = T[:, y, :] * M^T is 2 MMAs per tile, no data movement;
+//   y (tile index):    thread-local, 64 FMAs per register pair with the matrix in the constant bank;
+//   x (row index):     the tile is needed as the B operand, i.e. transposed across the warp:
+//                      4 shuffles per tile, then D = M * T[:, y, :] is 2 MMAs per tile.
+// All of interpolation, gradient, G, transposed gradient and transposed interpolation
+// (reference src/laplacian_gpu.hpp:175-420) are done in registers; shared memory only holds the
+// ring of asynchronous bulk copies (UBLKCP) that streams G, one y-tile (3 KB) per slot.
+// G is stored per cell as [y][comp][s][lane] (s = z & 1), i.e. in accumulator order.
+#pragma once
+
+#include <cstdint>
+
+#include "stiffness_slab.cuh"
+
+namespace bd
+{
+struct Mma8Tables
+{
+  double phi[64];  // Phi[q][i], 8 x 8, column 7 zero when nd = 7 (identity when nd = 8, qmode 0)
+  double dphi[64]; // dphi1[q][r], 8 x 8
+};
+
+constexpr int kMma8Stages = 4;
+constexpr int kMma8SlotBytes = 6 * 2 * 32 * 8; // one y-tile of G: 6 components x 2 registers x 32 lanes
+constexpr int kMma8WarpSmem = kMma8Stages * kMma8SlotBytes + 64;
+constexpr int kMma8Warps = 4;
+constexpr std::int64_t kMma8CellG = 8 * 6 * 2 * 32; // doubles of G per cell
+
+// Position of (cell pos, comp, q0, q1, q2) in the accumulator-order G layout.
+__host__ __device__ inline std::int64_t mma8_g_index(std::int64_t pos, int comp, int q0, int q1, int q2)
+{
+  const int lane = 4 * q0 + (q2 >> 1), s = q2 & 1;
+  return pos * kMma8CellG + ((static_cast<std::int64_t>(q1) * 6 + comp) * 2 + s) * 32 + lane;
+}
+
+__device__ __forceinline__ void dmma(double& d0, double& d1, double a, double b)
+{
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+      : "+d"(d0), "+d"(d1)
+      : "d"(a), "d"(b));
+}
+
+// Contraction over the column index z: out[x][z'] = sum_z t[x][z] M(z', z), bf[s] = M(g, 2t+s).
+__device__ __forceinline__ void mma8_col(double& o0, double& o1, double t0, double t1, const double (&bf)[2])
+{
+  o0 = 0;
+  o1 = 0;
+  dmma(o0, o1, t0, bf[0]);
+  dmma(o0, o1, t1, bf[1]);
+}
+
+// Contraction over the row index x: out[x'][z] = sum_x M(x', x) t[x][z], af[s] = M(g, 4s+t).
+__device__ __forceinline__ void mma8_row(double& o0, double& o1, double t0, double t1, const double (&af)[2],
+                                         int src0, int src1, bool odd)
+{
+  // B operand of k-step s: lane (g, t) needs t[4s + t][g], held by lane 4*(4s+t) + (g >> 1) in
+  // register (g & 1)
+  const double a0 = __shfl_sync(0xffffffffu, t0, src0), a1 = __shfl_sync(0xffffffffu, t1, src0);
+  const double c0 = __shfl_sync(0xffffffffu, t0, src1), c1 = __shfl_sync(0xffffffffu, t1, src1);
+  o0 = 0;
+  o1 = 0;
+  dmma(o0, o1, af[0], odd ? a1 : a0);
+  dmma(o0, o1, af[1], odd ? c1 : c0);
+}
+
+// Thread-local contraction over the tile index y: out[y'] = sum_y M[y'*8 + y] in[y] (TRANSPOSE: M[y*8 + y']).
+template <bool TRANSPOSE, bool ACCUMULATE>
+__device__ __forceinline__ void mma8_tile(const double (&M)[64], const double (&in)[8][2], double (&out)[8][2])
+{
+#pragma unroll
+  for (int yo = 0; yo < 8; ++yo)
+  {
+    double s0 = ACCUMULATE ? out[yo][0] : 0.0, s1 = ACCUMULATE ? out[yo][1] : 0.0;
+#pragma unroll
+    for (int yi = 0; yi < 8; ++yi)
+    {
+      const double m = TRANSPOSE ? M[yi * 8 + yo] : M[yo * 8 + yi];
+      s0 += m * in[yi][0];
+      s1 += m * in[yi][1];
+    }
+    out[yo][0] = s0;
+    out[yo][1] = s1;
+  }
+}
+
+template <int P, bool IDENTITY>
+__global__ void __launch_bounds__(kMma8Warps * 32)
+    stiffness_mma8_kernel(const double* __restrict__ u, double* __restrict__ y, const double* __restrict__ Gf,
+                          const double* __restrict__ cell_constants,
+                          const std::int32_t* __restrict__ mdofmap, const std::int32_t* __restrict__ cells,
+                          int ncells, const __grid_constant__ Mma8Tables tab)
+{
+  constexpr int ND = P + 1;
+  static_assert((ND == 7 && !IDENTITY) || (ND == 8 && IDENTITY), "nq = 8 only");
+  constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
+  constexpr int NSTAGE = kMma8Stages;
+  constexpr int SLOT = kMma8SlotBytes / 8;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  unsigned char* wbase = smem_raw + warp * kMma8WarpSmem;
+  double* ring = reinterpret_cast<double*>(wbase);
+  std::uint64_t* bars = reinterpret_cast<std::uint64_t*>(wbase + NSTAGE * kMma8SlotBytes);
+
+  // constant operand fragments
+  double phi_col[2], phiT_col[2], d_col[2], dT_col[2]; // B operands: M(g, 2t+s) / M^T(g, 2t+s)
+  double phi_row[2], phiT_row[2], d_row[2], dT_row[2]; // A operands: M(g, 4s+t) / M^T(g, 4s+t)
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+  {
+    phi_col[s] = tab.phi[g * 8 + 2 * t + s];
+    phiT_col[s] = tab.phi[(2 * t + s) * 8 + g];
+    d_col[s] = tab.dphi[g * 8 + 2 * t + s];
+    dT_col[s] = tab.dphi[(2 * t + s) * 8 + g];
+    phi_row[s] = tab.phi[g * 8 + 4 * s + t];
+    phiT_row[s] = tab.phi[(4 * s + t) * 8 + g];
+    d_row[s] = tab.dphi[g * 8 + 4 * s + t];
+    dT_row[s] = tab.dphi[(4 * s + t) * 8 + g];
+  }
+  const int src0 = 4 * t + (g >> 1), src1 = 4 * (4 + t) + (g >> 1);
+  const bool odd = g & 1;
+
+  const int warps_total = gridDim.x * kMma8Warps;
+  const int first = blockIdx.x * kMma8Warps + warp;
+  const int my_cells = first < ncells ? (ncells - first + warps_total - 1) / warps_total : 0;
+  const int total_slots = my_cells * 8;
+
+  if (lane == 0)
+  {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s)
+      mbar_init(bars + s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  auto issue = [&](int s) {
+    const int k = s >> 3, tile = s & 7;
+    const std::int64_t pos = first + static_cast<std::int64_t>(k) * warps_total;
+    const double* src = Gf + pos * kMma8CellG + static_cast<std::int64_t>(tile) * SLOT;
+    const int st = s % NSTAGE;
+    mbar_expect_tx(bars + st, kMma8SlotBytes);
+    bulk_copy_g2s(ring + st * SLOT, src, kMma8SlotBytes, bars + st);
+  };
+  if (lane == 0)
+    for (int s = 0; s < NSTAGE - 1 && s < total_slots; ++s)
+      issue(s);
+
+  int slot = 0;
+  for (int k = 0; k < my_cells; ++k)
+  {
+    const int pos = first + k * warps_total;
+    const std::int32_t* row = mdofmap + static_cast<std::int64_t>(cells[pos]) * ND3;
+
+    // ---- gather: T[x = g][y][z = 2t + s], zero outside the ND^3 dofs and on constrained dofs
+    std::int32_t dof[8][2];
+    double T[8][2];
+#pragma unroll
+    for (int yy = 0; yy < 8; ++yy)
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+      {
+        const int z = 2 * t + s;
+        const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
+        dof[yy][s] = valid ? row[(g * ND + yy) * ND + z] : kBcBit;
+      }
+#pragma unroll
+    for (int yy = 0; yy < 8; ++yy)
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+      {
+        const int z = 2 * t + s;
+        const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
+        double v = 0;
+        if (valid)
+        {
+          v = u[dof[yy][s] & 0x7fffffff];
+          if (dof[yy][s] < 0)
+          {
+            y[dof[yy][s] & 0x7fffffff] = v; // b[dof] = u[dof] on constrained dofs (reference :163-166)
+            v = 0;
+          }
+        }
+        T[yy][s] = v;
+      }
+
+    // ---- interpolation to the quadrature points (reference :175-211)
+    if constexpr (!IDENTITY)
+    {
+      double W[8][2];
+#pragma unroll
+      for (int yy = 0; yy < 8; ++yy)
+        mma8_col(W[yy][0], W[yy][1], T[yy][0], T[yy][1], phi_col); // z
+      mma8_tile<false, false>(tab.phi, W, T);                      // y
+#pragma unroll
+      for (int yy = 0; yy < 8; ++yy)
+      {
+        double o0, o1;
+        mma8_row(o0, o1, T[yy][0], T[yy][1], phi_row, src0, src1, odd); // x
+        T[yy][0] = o0;
+        T[yy][1] = o1;
+      }
+    }
+
+    // ---- gradient, G, transposed gradient (reference :239-314), tile by tile
+    double F[8][2]; // g_y, then f_y
+    mma8_tile<false, false>(tab.dphi, T, F);
+    double R[8][2];
+    const double kappa = cell_constants[pos];
+#pragma unroll
+    for (int yy = 0; yy < 8; ++yy, ++slot)
+    {
+      if (lane == 0 && slot + NSTAGE - 1 < total_slots)
+        issue(slot + NSTAGE - 1);
+      double gx0, gx1, gz0, gz1;
+      mma8_row(gx0, gx1, T[yy][0], T[yy][1], d_row, src0, src1, odd);
+      mma8_col(gz0, gz1, T[yy][0], T[yy][1], d_col);
+      const int st = slot % NSTAGE;
+      mbar_wait(bars + st, (slot / NSTAGE) & 1);
+      const double* gs = ring + st * SLOT + lane; // [comp][s][lane]
+      double fx[2], fz[2];
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+      {
+        const double G0 = gs[(0 * 2 + s) * 32], G1 = gs[(1 * 2 + s) * 32], G2 = gs[(2 * 2 + s) * 32];
+        const double G3 = gs[(3 * 2 + s) * 32], G4 = gs[(4 * 2 + s) * 32], G5 = gs[(5 * 2 + s) * 32];
+        const double gx = s ? gx1 : gx0, gy = F[yy][s], gz = s ? gz1 : gz0;
+        fx[s] = kappa * (G0 * gx + G1 * gy + G2 * gz);
+        F[yy][s] = kappa * (G1 * gx + G3 * gy + G4 * gz);
+        fz[s] = kappa * (G2 * gx + G4 * gy + G5 * gz);
+      }
+      __syncwarp(); // every lane is done with slot `st` before it is refilled
+      double rx0, rx1, rz0, rz1;
+      mma8_row(rx0, rx1, fx[0], fx[1], dT_row, src0, src1, odd);
+      mma8_col(rz0, rz1, fz[0], fz[1], dT_col);
+      R[yy][0] = rx0 + rz0;
+      R[yy][1] = rx1 + rz1;
+    }
+    mma8_tile<true, true>(tab.dphi, F, R);
+
+    // ---- transposed interpolation (reference :388-420)
+    if constexpr (!IDENTITY)
+    {
+      double W[8][2];
+#pragma unroll
+      for (int yy = 0; yy < 8; ++yy)
+        mma8_col(W[yy][0], W[yy][1], R[yy][0], R[yy][1], phiT_col); // z
+      mma8_tile<true, false>(tab.phi, W, R);                       // y
+#pragma unroll
+      for (int yy = 0; yy < 8; ++yy)
+      {
+        double o0, o1;
+        mma8_row(o0, o1, R[yy][0], R[yy][1], phiT_row, src0, src1, odd); // x
+        R[yy][0] = o0;
+        R[yy][1] = o1;
+      }
+    }
+
+    // ---- scatter-add (reference :424-425)
+#pragma unroll
+    for (int yy = 0; yy < 8; ++yy)
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+        if (dof[yy][s] >= 0)
+          atomicAdd(y + dof[yy][s], R[yy][s]);
+  }
+}
+
+// Geometry tensor in accumulator order from the reference layout (tests) and back.
+__global__ void __launch_bounds__(256)
+    mma8_g_to_reference_kernel(const double* __restrict__ Gf, double* __restrict__ G, std::int64_t ncells);
+
+} // namespace bd

@@ -104,12 +104,227 @@ inline std::int64_t slab_g_size(int nq, std::int64_t ncells)
   return (ncells + cw - 1) / cw * (static_cast<std::int64_t>(nq) * nq * 6 * cw * nq);
 }
 
-template <typename T>
-__device__ __forceinline__ T ld_stream(const T* p)
+// ------------------------------------------------------------------------------------------------
+// The three compute phases, shared by the two kernels below.
+// Cube element (k3, q1, i, row r): cube[k3*CUBE + (q1*ND + i)*RL + r], r = c*NQ + q2.
+// ------------------------------------------------------------------------------------------------
+
+// Forward X phase of lane (c, i): y/z contractions of the dof plane `ul` -> a_x, a_y, a_z in the cube.
+template <typename T, int ND, int NQ, int RL, int CUBE, bool IDENTITY>
+__device__ __forceinline__ void slab_forward_x(const SlabTables<T, ND, NQ>& tab, const T (&ul)[ND * ND],
+                                               T* __restrict__ dst0)
 {
-  return __ldg(p);
+  // dst0 = cube + i*RL + rbase ; element (q1, q2) at dst0[q1*ND*RL + q2]
+#pragma unroll
+  for (int q2 = 0; q2 < NQ; ++q2)
+  {
+    T pz[ND], dz[ND];
+#pragma unroll
+    for (int j = 0; j < ND; ++j)
+    {
+      if constexpr (IDENTITY)
+      {
+        pz[j] = ul[j * ND + q2];
+        T s = 0;
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+          s += tab.dphi[q2 * ND + k] * ul[j * ND + k];
+        dz[j] = s;
+      }
+      else
+      {
+        T s = 0, d = 0;
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+        {
+          s += tab.phi[q2 * ND + k] * ul[j * ND + k];
+          d += tab.dphi[q2 * ND + k] * ul[j * ND + k];
+        }
+        pz[j] = s;
+        dz[j] = d;
+      }
+    }
+#pragma unroll
+    for (int q1 = 0; q1 < NQ; ++q1)
+    {
+      T ax, ay = 0, az;
+      if constexpr (IDENTITY)
+      {
+        ax = pz[q1];
+        az = dz[q1];
+#pragma unroll
+        for (int j = 0; j < ND; ++j)
+          ay += tab.dphi[q1 * ND + j] * pz[j];
+      }
+      else
+      {
+        ax = 0;
+        az = 0;
+#pragma unroll
+        for (int j = 0; j < ND; ++j)
+        {
+          ax += tab.phi[q1 * ND + j] * pz[j];
+          ay += tab.dphi[q1 * ND + j] * pz[j];
+          az += tab.phi[q1 * ND + j] * dz[j];
+        }
+      }
+      T* dst = dst0 + q1 * (ND * RL) + q2;
+      dst[0] = ax;
+      dst[CUBE] = ay;
+      dst[2 * CUBE] = az;
+    }
+  }
 }
 
+// Z phase of lane (c, q2) for one q1 and the q0 range [Q0B, Q0B + Q0N): x contractions, G, kappa,
+// transposed x contractions accumulated into bx, by, bz.  G values come from `g` (global or shared
+// memory), element (q0 - Q0B, comp) at g[((q0 - Q0B)*6 + comp)*ROW].
+template <typename T, int ND, int NQ, int ROW, bool IDENTITY, int Q0B, int Q0N, bool STREAM_LDG>
+__device__ __forceinline__ void slab_z_points(const SlabTables<T, ND, NQ>& tab, const T (&ax)[ND],
+                                              const T (&ay)[ND], const T (&az)[ND], T (&bx)[ND],
+                                              T (&by)[ND], T (&bz)[ND], const T* __restrict__ g, T kappa)
+{
+#pragma unroll
+  for (int qq = 0; qq < Q0N; ++qq)
+  {
+    constexpr int dummy = 0;
+    (void)dummy;
+    const int q0 = Q0B + qq;
+    const T* gp = g + qq * (6 * ROW);
+    T G0, G1, G2, G3, G4, G5;
+    if constexpr (STREAM_LDG)
+    {
+      G0 = __ldg(gp + 0 * ROW);
+      G1 = __ldg(gp + 1 * ROW);
+      G2 = __ldg(gp + 2 * ROW);
+      G3 = __ldg(gp + 3 * ROW);
+      G4 = __ldg(gp + 4 * ROW);
+      G5 = __ldg(gp + 5 * ROW);
+    }
+    else
+    {
+      G0 = gp[0 * ROW];
+      G1 = gp[1 * ROW];
+      G2 = gp[2 * ROW];
+      G3 = gp[3 * ROW];
+      G4 = gp[4 * ROW];
+      G5 = gp[5 * ROW];
+    }
+    T gx = 0, gy, gz;
+    if constexpr (IDENTITY)
+    {
+      gy = ay[q0];
+      gz = az[q0];
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+        gx += tab.dphi[q0 * ND + i] * ax[i];
+    }
+    else
+    {
+      gy = 0;
+      gz = 0;
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+      {
+        gx += tab.dphi[q0 * ND + i] * ax[i];
+        gy += tab.phi[q0 * ND + i] * ay[i];
+        gz += tab.phi[q0 * ND + i] * az[i];
+      }
+    }
+    // reference src/laplacian_gpu.hpp:269-273
+    const T fx = kappa * (G0 * gx + G1 * gy + G2 * gz);
+    const T fy = kappa * (G1 * gx + G3 * gy + G4 * gz);
+    const T fz = kappa * (G2 * gx + G4 * gy + G5 * gz);
+    if constexpr (IDENTITY)
+    {
+      by[q0] = fy;
+      bz[q0] = fz;
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+        bx[i] += tab.dphi[q0 * ND + i] * fx;
+    }
+    else
+    {
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+      {
+        bx[i] += tab.dphi[q0 * ND + i] * fx;
+        by[i] += tab.phi[q0 * ND + i] * fy;
+        bz[i] += tab.phi[q0 * ND + i] * fz;
+      }
+    }
+  }
+}
+
+// Backward X phase of lane (c, i): transposed y/z contractions of b_x, b_y, b_z -> out (dof plane i).
+template <typename T, int ND, int NQ, int RL, int CUBE, bool IDENTITY>
+__device__ __forceinline__ void slab_backward_x(const SlabTables<T, ND, NQ>& tab, const T* __restrict__ src0,
+                                                T (&out)[ND * ND])
+{
+#pragma unroll
+  for (int t = 0; t < ND * ND; ++t)
+    out[t] = 0;
+#pragma unroll
+  for (int q2 = 0; q2 < NQ; ++q2)
+  {
+    T e1[ND], e2[ND];
+#pragma unroll
+    for (int j = 0; j < ND; ++j)
+    {
+      e1[j] = 0;
+      e2[j] = 0;
+    }
+#pragma unroll
+    for (int q1 = 0; q1 < NQ; ++q1)
+    {
+      const T* src = src0 + q1 * (ND * RL) + q2;
+      const T bx = src[0], by = src[CUBE], bz = src[2 * CUBE];
+      if constexpr (IDENTITY)
+      {
+        e1[q1] += bx;
+        e2[q1] += bz;
+#pragma unroll
+        for (int j = 0; j < ND; ++j)
+          e1[j] += tab.dphi[q1 * ND + j] * by;
+      }
+      else
+      {
+#pragma unroll
+        for (int j = 0; j < ND; ++j)
+        {
+          e1[j] += tab.phi[q1 * ND + j] * bx;
+          e1[j] += tab.dphi[q1 * ND + j] * by;
+          e2[j] += tab.phi[q1 * ND + j] * bz;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < ND; ++j)
+    {
+      if constexpr (IDENTITY)
+      {
+        out[j * ND + q2] += e1[j];
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+          out[j * ND + k] += tab.dphi[q2 * ND + k] * e2[j];
+      }
+      else
+      {
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+        {
+          out[j * ND + k] += tab.phi[q2 * ND + k] * e1[j];
+          out[j * ND + k] += tab.dphi[q2 * ND + k] * e2[j];
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Plain kernel: G loaded straight from global memory (kept as the fallback for configurations the
+// asynchronous-copy kernel does not cover, and for comparison: BD_STIFFNESS_VARIANT=slab).
+// ------------------------------------------------------------------------------------------------
 template <typename T, int P, int NQ, bool IDENTITY>
 __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
     stiffness_slab_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ Gs,
@@ -131,7 +346,6 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
   const int m = lane - c * NQ;    // team member: dof plane i (X phases) / point plane q2 (Z phase)
   const bool lane_ok = c < CW;
   T* cube = smem + warp * (3 * CUBE);
-  // element (k3, q1, i, row r): cube[k3*CUBE + (q1*ND + i)*RL + r], r = c*NQ + q2
   const int rbase = (lane_ok ? c : 0) * NQ;
 
   const int nbatches = (ncells + CW - 1) / CW;
@@ -142,7 +356,7 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
     const bool active = lane_ok && pos < ncells;
     const bool xlane = active && m < ND; // lanes that own a dof plane
 
-    // ------------------------------------------------------------------ gather (X layout)
+    // gather (reference :153-170)
     std::int32_t dof[ND2];
     T ul[ND2];
     if (xlane)
@@ -157,91 +371,17 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
         const T v = u[dof[t]];
         if (bc[dof[t]])
         {
-          y[dof[t]] = v; // b[dof] = u[dof] on constrained dofs (reference :163-166)
+          y[dof[t]] = v; // b[dof] = u[dof] on constrained dofs
           dof[t] = -1;
           ul[t] = 0;
         }
         else
           ul[t] = v;
       }
-    }
-    else
-    {
-#pragma unroll
-      for (int t = 0; t < ND2; ++t)
-      {
-        dof[t] = -1;
-        ul[t] = 0;
-      }
-    }
-
-    // ------------------------------------------------------------------ forward X phase
-    // stream over q2: column of Phi_z u / DPhi_z u, then the y contraction, then store
-    if (xlane)
-    {
-#pragma unroll
-      for (int q2 = 0; q2 < NQ; ++q2)
-      {
-        T pz[ND], dz[ND];
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
-        {
-          if constexpr (IDENTITY)
-          {
-            pz[j] = ul[j * ND + q2];
-            T s = 0;
-#pragma unroll
-            for (int k = 0; k < ND; ++k)
-              s += tab.dphi[q2 * ND + k] * ul[j * ND + k];
-            dz[j] = s;
-          }
-          else
-          {
-            T s = 0, d = 0;
-#pragma unroll
-            for (int k = 0; k < ND; ++k)
-            {
-              s += tab.phi[q2 * ND + k] * ul[j * ND + k];
-              d += tab.dphi[q2 * ND + k] * ul[j * ND + k];
-            }
-            pz[j] = s;
-            dz[j] = d;
-          }
-        }
-#pragma unroll
-        for (int q1 = 0; q1 < NQ; ++q1)
-        {
-          T ax, ay = 0, az;
-          if constexpr (IDENTITY)
-          {
-            ax = pz[q1];
-            az = dz[q1];
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-              ay += tab.dphi[q1 * ND + j] * pz[j];
-          }
-          else
-          {
-            ax = 0;
-            az = 0;
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-            {
-              ax += tab.phi[q1 * ND + j] * pz[j];
-              ay += tab.dphi[q1 * ND + j] * pz[j];
-              az += tab.phi[q1 * ND + j] * dz[j];
-            }
-          }
-          T* dst = cube + (q1 * ND + m) * RL + rbase + q2;
-          dst[0] = ax;
-          dst[CUBE] = ay;
-          dst[2 * CUBE] = az;
-        }
-      }
+      slab_forward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, ul, cube + m * RL + rbase);
     }
     __syncwarp();
 
-    // ------------------------------------------------------------------ Z phase: x contractions + G
     if (active)
     {
       const T kappa = cell_constants[pos];
@@ -250,7 +390,7 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
 #pragma unroll(NQ <= 5 ? NQ : 1)
       for (int q1 = 0; q1 < NQ; ++q1)
       {
-        T ax[ND], ay[ND], az[ND];
+        T ax[ND], ay[ND], az[ND], bx[ND], by[ND], bz[ND];
         T* src = cube + (q1 * ND) * RL + rbase + m;
 #pragma unroll
         for (int i = 0; i < ND; ++i)
@@ -258,69 +398,12 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
           ax[i] = src[i * RL];
           ay[i] = src[i * RL + CUBE];
           az[i] = src[i * RL + 2 * CUBE];
-        }
-        T bx[ND], by[ND], bz[ND];
-#pragma unroll
-        for (int i = 0; i < ND; ++i)
-        {
           bx[i] = 0;
           by[i] = 0;
           bz[i] = 0;
         }
-#pragma unroll
-        for (int q0 = 0; q0 < NQ; ++q0)
-        {
-          const T* g = Gb + (static_cast<std::int64_t>(q1) * NQ + q0) * (6 * C::ROW);
-          const T G0 = ld_stream(g + 0 * C::ROW);
-          const T G1 = ld_stream(g + 1 * C::ROW);
-          const T G2 = ld_stream(g + 2 * C::ROW);
-          const T G3 = ld_stream(g + 3 * C::ROW);
-          const T G4 = ld_stream(g + 4 * C::ROW);
-          const T G5 = ld_stream(g + 5 * C::ROW);
-          T gx = 0, gy, gz;
-          if constexpr (IDENTITY)
-          {
-            gy = ay[q0];
-            gz = az[q0];
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-              gx += tab.dphi[q0 * ND + i] * ax[i];
-          }
-          else
-          {
-            gy = 0;
-            gz = 0;
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-            {
-              gx += tab.dphi[q0 * ND + i] * ax[i];
-              gy += tab.phi[q0 * ND + i] * ay[i];
-              gz += tab.phi[q0 * ND + i] * az[i];
-            }
-          }
-          // reference :269-273
-          const T fx = kappa * (G0 * gx + G1 * gy + G2 * gz);
-          const T fy = kappa * (G1 * gx + G3 * gy + G4 * gz);
-          const T fz = kappa * (G2 * gx + G4 * gy + G5 * gz);
-          if constexpr (IDENTITY)
-          {
-            by[q0] = fy;
-            bz[q0] = fz;
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-              bx[i] += tab.dphi[q0 * ND + i] * fx;
-          }
-          else
-          {
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-            {
-              bx[i] += tab.dphi[q0 * ND + i] * fx;
-              by[i] += tab.phi[q0 * ND + i] * fy;
-              bz[i] += tab.phi[q0 * ND + i] * fz;
-            }
-          }
-        }
+        slab_z_points<T, ND, NQ, C::ROW, IDENTITY, 0, NQ, true>(
+            tab, ax, ay, az, bx, by, bz, Gb + static_cast<std::int64_t>(q1) * (NQ * 6 * C::ROW), kappa);
 #pragma unroll
         for (int i = 0; i < ND; ++i)
         {
@@ -332,68 +415,10 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
     }
     __syncwarp();
 
-    // ------------------------------------------------------------------ backward X phase + scatter
     if (xlane)
     {
       T out[ND2];
-#pragma unroll
-      for (int t = 0; t < ND2; ++t)
-        out[t] = 0;
-#pragma unroll
-      for (int q2 = 0; q2 < NQ; ++q2)
-      {
-        T e1[ND], e2[ND];
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
-        {
-          e1[j] = 0;
-          e2[j] = 0;
-        }
-#pragma unroll
-        for (int q1 = 0; q1 < NQ; ++q1)
-        {
-          const T* src = cube + (q1 * ND + m) * RL + rbase + q2;
-          const T bx = src[0], by = src[CUBE], bz = src[2 * CUBE];
-          if constexpr (IDENTITY)
-          {
-            e1[q1] += bx;
-            e2[q1] += bz;
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-              e1[j] += tab.dphi[q1 * ND + j] * by;
-          }
-          else
-          {
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-            {
-              e1[j] += tab.phi[q1 * ND + j] * bx;
-              e1[j] += tab.dphi[q1 * ND + j] * by;
-              e2[j] += tab.phi[q1 * ND + j] * bz;
-            }
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
-        {
-          if constexpr (IDENTITY)
-          {
-            out[j * ND + q2] += e1[j];
-#pragma unroll
-            for (int k = 0; k < ND; ++k)
-              out[j * ND + k] += tab.dphi[q2 * ND + k] * e2[j];
-          }
-          else
-          {
-#pragma unroll
-            for (int k = 0; k < ND; ++k)
-            {
-              out[j * ND + k] += tab.phi[q2 * ND + k] * e1[j];
-              out[j * ND + k] += tab.dphi[q2 * ND + k] * e2[j];
-            }
-          }
-        }
-      }
+      slab_backward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, cube + m * RL + rbase, out);
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
         if (dof[t] >= 0)
@@ -403,18 +428,23 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
   }
 }
 
-// ---------------------------------------------------------------------------------------------
-// Asynchronous-copy variant: the G stream is decoupled from the math.
+// ------------------------------------------------------------------------------------------------
+// Asynchronous-copy kernel: the G stream is decoupled from the math.
 //
-// ncu on the plain slab kernel (profiles/r1_v2_*) shows it purely latency bound: 11.6 of 14.9
-// cycles between issues are "long scoreboard" (waiting for G / gather loads) at 12 warps per SM.
-// Here every warp keeps a ring of NSTAGE shared-memory slots and one elected lane streams the
-// batch's G through it with 1-D bulk asynchronous copies (cp.async.bulk -> UBLKCP, completion on
-// an mbarrier): one slot = one q1 slice of the batch (NQ*6*ROW scalars, contiguous in the slab
-// layout), NSTAGE-1 slices are always in flight, and the stream runs on across batch boundaries,
-// so the next batch's first slices arrive while the current batch is still in its backward phase.
-// The dof indices and input values of the next batch are prefetched into registers the same way.
-// ---------------------------------------------------------------------------------------------
+// ncu on the plain kernel (profiles/r1_v2_*) shows it purely latency bound: 11.6 of 14.9 cycles
+// between issues are "long scoreboard" (waiting for G / gather loads) at 12 warps per SM.  Here
+// every warp keeps a ring of NSTAGE shared-memory slots and one elected lane streams the batch's G
+// through it with 1-D bulk asynchronous copies (cp.async.bulk -> UBLKCP, completion on an
+// mbarrier).  One slot = Q0C consecutive q0 rows of one q1 slice (contiguous in the slab layout);
+// NSTAGE-1 slots are always in flight and the stream runs on across batch boundaries, so the next
+// batch's first slots arrive while the current batch is still in its backward phase.
+//
+// The kernel reads a *masked dofmap*: the cell dofmap with the BC marker of each dof folded into
+// bit 31 (built once per operator), which removes the dependent byte gather bc[dof] from the hot
+// loop.  With PREFETCH the dof indices and input values of the next batch are loaded into
+// registers one phase ahead; without it (large ND, register budget) the indices are simply
+// re-read before the scatter (they are L1/L2 hits).
+// ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ std::uint32_t smem_addr(const void* p)
 {
   return static_cast<std::uint32_t>(__cvta_generic_to_shared(p));
@@ -450,34 +480,38 @@ __device__ __forceinline__ void mbar_wait(std::uint64_t* bar, std::uint32_t pari
                : "memory");
 }
 
-template <typename T, int P, int NQ, int NSTAGE>
+constexpr std::int32_t kBcBit = static_cast<std::int32_t>(0x80000000u);
+
+template <typename T, int P, int NQ, int NSTAGE, int Q0C, int WARPS_>
 struct SlabTmaConfig
 {
   using Base = SlabConfig<T, P, NQ>;
-  static constexpr int SLICE = NQ * 6 * Base::ROW;                 // scalars per q1 slice of a batch
-  static constexpr int SLICE_BYTES = SLICE * int(sizeof(T));
+  static_assert(NQ % Q0C == 0 && NQ / Q0C <= 4, "Q0C must divide NQ into at most 4 chunks");
+  static constexpr int NCH = NQ / Q0C;                            // slots per q1 slice
+  static constexpr int SLOT = Q0C * 6 * Base::ROW;                // scalars per slot
+  static constexpr int SLOT_BYTES = SLOT * int(sizeof(T));
   static constexpr int CUBE_BYTES = (3 * Base::CUBE * int(sizeof(T)) + 15) / 16 * 16;
-  static constexpr int WARP_SMEM = CUBE_BYTES + NSTAGE * SLICE_BYTES + 64; // + mbarriers
-  static constexpr int MAX_SMEM = 225 * 1024;
-  static constexpr int WARPS = WARP_SMEM * 2 + 2048 <= MAX_SMEM ? 2 : 1;
+  static constexpr int WARP_SMEM = CUBE_BYTES + NSTAGE * SLOT_BYTES + 64; // + mbarriers
+  static constexpr int MAX_SMEM = 226 * 1024;
+  static constexpr int WARPS = WARPS_;
   static constexpr int THREADS = WARPS * 32;
   static constexpr int CTA_SMEM = WARPS * WARP_SMEM;
-  static constexpr bool SUPPORTED = (SLICE_BYTES % 16 == 0) && (WARP_SMEM + 1024 <= MAX_SMEM);
+  static constexpr bool SUPPORTED = (SLOT_BYTES % 16 == 0) && (CTA_SMEM <= MAX_SMEM);
 };
 
-template <typename T, int P, int NQ, bool IDENTITY, int NSTAGE>
-__global__ void __launch_bounds__(SlabTmaConfig<T, P, NQ, NSTAGE>::THREADS)
+template <typename T, int P, int NQ, bool IDENTITY, int NSTAGE, int Q0C, int WARPS_, bool PREFETCH>
+__global__ void __launch_bounds__(WARPS_ * 32)
     stiffness_slab_tma_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ Gs,
                               const T* __restrict__ cell_constants,
-                              const std::int32_t* __restrict__ dofmap,
+                              const std::int32_t* __restrict__ mdofmap,
                               const std::int32_t* __restrict__ cells, int ncells,
-                              const std::int8_t* __restrict__ bc,
                               const __grid_constant__ SlabTables<T, P + 1, NQ> tab)
 {
   using C = SlabConfig<T, P, NQ>;
-  using TC = SlabTmaConfig<T, P, NQ, NSTAGE>;
+  using TC = SlabTmaConfig<T, P, NQ, NSTAGE, Q0C, WARPS_>;
   constexpr int ND = C::ND, CW = C::CW, RL = C::RL, CUBE = C::CUBE, ROW = C::ROW;
   constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
+  constexpr int NCH = TC::NCH;
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;
@@ -488,14 +522,14 @@ __global__ void __launch_bounds__(SlabTmaConfig<T, P, NQ, NSTAGE>::THREADS)
   unsigned char* wbase = smem_raw + warp * TC::WARP_SMEM;
   T* cube = reinterpret_cast<T*>(wbase);
   T* ring = reinterpret_cast<T*>(wbase + TC::CUBE_BYTES);
-  std::uint64_t* bars = reinterpret_cast<std::uint64_t*>(wbase + TC::CUBE_BYTES + NSTAGE * TC::SLICE_BYTES);
+  std::uint64_t* bars = reinterpret_cast<std::uint64_t*>(wbase + TC::CUBE_BYTES + NSTAGE * TC::SLOT_BYTES);
   const int rbase = (lane_ok ? c : 0) * NQ;
 
   const int nbatches = (ncells + CW - 1) / CW;
   const int warps_total = gridDim.x * TC::WARPS;
   const int first = blockIdx.x * TC::WARPS + warp;
   const int my_batches = first < nbatches ? (nbatches - first + warps_total - 1) / warps_total : 0;
-  const int total_slices = my_batches * NQ;
+  const int total_slots = my_batches * NQ * NCH;
 
   if (lane == 0)
   {
@@ -506,168 +540,92 @@ __global__ void __launch_bounds__(SlabTmaConfig<T, P, NQ, NSTAGE>::THREADS)
   }
   __syncwarp();
 
-  // slice s of this warp's stream = (batch first + (s / NQ) * warps_total, q1 = s % NQ)
+  // slot s of this warp's stream = (batch first + k*warps_total, q1, chunk), s = (k*NQ + q1)*NCH + chunk;
+  // within a batch the slots are consecutive in memory
   auto issue = [&](int s) {
-    const int k = s / NQ, q1 = s - k * NQ;
+    const int k = s / (NQ * NCH), r = s - k * (NQ * NCH);
     const std::int64_t batch = first + static_cast<std::int64_t>(k) * warps_total;
-    const T* src = Gs + batch * C::G_BATCH + static_cast<std::int64_t>(q1) * TC::SLICE;
+    const T* src = Gs + batch * C::G_BATCH + static_cast<std::int64_t>(r) * TC::SLOT;
     const int st = s % NSTAGE;
-    mbar_expect_tx(bars + st, TC::SLICE_BYTES);
-    bulk_copy_g2s(ring + st * TC::SLICE, src, TC::SLICE_BYTES, bars + st);
+    mbar_expect_tx(bars + st, TC::SLOT_BYTES);
+    bulk_copy_g2s(ring + st * TC::SLOT, src, TC::SLOT_BYTES, bars + st);
   };
   if (lane == 0)
   {
-    for (int s = 0; s < NSTAGE - 1 && s < total_slices; ++s)
+    for (int s = 0; s < NSTAGE - 1 && s < total_slots; ++s)
       issue(s);
   }
 
-  // dof indices / inputs of the current batch (prefetched one batch ahead)
-  std::int32_t dof[ND2];
-  T ul[ND2];
-  std::int8_t flag[ND2];
-  auto load_dofs = [&](int batch, std::int32_t (&d)[ND2]) {
+  auto row_of = [&](int batch) -> const std::int32_t* {
     const int pos = batch * CW + c;
-    const bool x = lane_ok && pos < ncells && m < ND && batch < nbatches;
-    if (x)
-    {
-      const std::int32_t* row = dofmap + static_cast<std::int64_t>(cells[pos]) * ND3 + m * ND2;
-#pragma unroll
-      for (int t = 0; t < ND2; ++t)
-        d[t] = row[t];
-    }
-    else
-    {
-#pragma unroll
-      for (int t = 0; t < ND2; ++t)
-        d[t] = -1;
-    }
+    const bool x = lane_ok && batch < nbatches && pos < ncells && m < ND;
+    return x ? mdofmap + static_cast<std::int64_t>(cells[pos]) * ND3 + m * ND2 : nullptr;
   };
-  auto load_values = [&](const std::int32_t (&d)[ND2], T (&v)[ND2], std::int8_t (&f)[ND2]) {
+  auto load_dofs = [&](const std::int32_t* row, std::int32_t (&d)[ND2]) {
 #pragma unroll
     for (int t = 0; t < ND2; ++t)
-    {
-      if (d[t] >= 0)
-      {
-        v[t] = u[d[t]];
-        f[t] = bc[d[t]];
-      }
-      else
-      {
-        v[t] = 0;
-        f[t] = 0;
-      }
-    }
+      d[t] = row ? row[t] : kBcBit; // inactive lanes look like constrained dofs: no gather, no scatter
   };
-  if (my_batches > 0)
+  auto load_values = [&](const std::int32_t* row, const std::int32_t (&d)[ND2], T (&v)[ND2]) {
+#pragma unroll
+    for (int t = 0; t < ND2; ++t)
+      v[t] = row ? u[d[t] & 0x7fffffff] : T(0);
+  };
+
+  std::int32_t dof[ND2];
+  T ul[ND2];
+  if constexpr (PREFETCH)
   {
-    load_dofs(first, dof);
-    load_values(dof, ul, flag);
+    const std::int32_t* row = row_of(first);
+    load_dofs(row, dof);
+    load_values(row, dof, ul);
   }
 
-  int slice = 0;
+  int slot = 0;
   for (int k = 0; k < my_batches; ++k)
   {
     const int batch = first + k * warps_total;
     const int pos = batch * CW + c;
     const bool active = lane_ok && pos < ncells;
     const bool xlane = active && m < ND;
+    const std::int32_t* row = row_of(batch);
 
-    // BC masking of the gathered values (reference :163-169)
-#pragma unroll
-    for (int t = 0; t < ND2; ++t)
+    if constexpr (!PREFETCH)
     {
-      if (flag[t])
-      {
-        y[dof[t]] = ul[t];
-        dof[t] = -1;
-        ul[t] = 0;
-      }
+      load_dofs(row, dof);
+      load_values(row, dof, ul);
     }
-
-    // ------------------------------------------------------------------ forward X phase
+    // BC masking (reference :163-169): b[dof] = u[dof], the dof contributes 0 and receives nothing
     if (xlane)
     {
 #pragma unroll
-      for (int q2 = 0; q2 < NQ; ++q2)
-      {
-        T pz[ND], dz[ND];
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
+      for (int t = 0; t < ND2; ++t)
+        if (dof[t] < 0)
         {
-          if constexpr (IDENTITY)
-          {
-            pz[j] = ul[j * ND + q2];
-            T s = 0;
-#pragma unroll
-            for (int kk = 0; kk < ND; ++kk)
-              s += tab.dphi[q2 * ND + kk] * ul[j * ND + kk];
-            dz[j] = s;
-          }
-          else
-          {
-            T s = 0, d = 0;
-#pragma unroll
-            for (int kk = 0; kk < ND; ++kk)
-            {
-              s += tab.phi[q2 * ND + kk] * ul[j * ND + kk];
-              d += tab.dphi[q2 * ND + kk] * ul[j * ND + kk];
-            }
-            pz[j] = s;
-            dz[j] = d;
-          }
+          y[dof[t] & 0x7fffffff] = ul[t];
+          ul[t] = 0;
         }
-#pragma unroll
-        for (int q1 = 0; q1 < NQ; ++q1)
-        {
-          T ax, ay = 0, az;
-          if constexpr (IDENTITY)
-          {
-            ax = pz[q1];
-            az = dz[q1];
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-              ay += tab.dphi[q1 * ND + j] * pz[j];
-          }
-          else
-          {
-            ax = 0;
-            az = 0;
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-            {
-              ax += tab.phi[q1 * ND + j] * pz[j];
-              ay += tab.dphi[q1 * ND + j] * pz[j];
-              az += tab.phi[q1 * ND + j] * dz[j];
-            }
-          }
-          T* dst = cube + (q1 * ND + m) * RL + rbase + q2;
-          dst[0] = ax;
-          dst[CUBE] = ay;
-          dst[2 * CUBE] = az;
-        }
-      }
+      slab_forward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, ul, cube + m * RL + rbase);
     }
     __syncwarp();
 
     // next batch's dof indices: in flight during the whole middle phase
-    std::int32_t ndof[ND2];
-    load_dofs(batch + warps_total, ndof);
+    std::int32_t ndof[PREFETCH ? ND2 : 1];
+    const std::int32_t* nrow = nullptr;
+    if constexpr (PREFETCH)
+    {
+      nrow = row_of(batch + warps_total);
+      load_dofs(nrow, ndof);
+    }
 
-    // ------------------------------------------------------------------ Z phase
     const T kappa = active ? cell_constants[pos] : T(0);
 #pragma unroll 1
-    for (int q1 = 0; q1 < NQ; ++q1, ++slice)
+    for (int q1 = 0; q1 < NQ; ++q1)
     {
-      // refill the slot consumed one step ago with the slice NSTAGE-1 ahead
-      if (lane == 0 && slice + NSTAGE - 1 < total_slices)
-        issue(slice + NSTAGE - 1);
-      const int st = slice % NSTAGE;
-      mbar_wait(bars + st, (slice / NSTAGE) & 1);
+      T ax[ND], ay[ND], az[ND], bx[ND], by[ND], bz[ND];
+      T* src = cube + (q1 * ND) * RL + rbase + m;
       if (active)
       {
-        const T* gs = ring + st * TC::SLICE + rbase + m;
-        T ax[ND], ay[ND], az[ND];
-        T* src = cube + (q1 * ND) * RL + rbase + m;
 #pragma unroll
         for (int i = 0; i < ND; ++i)
         {
@@ -675,63 +633,50 @@ __global__ void __launch_bounds__(SlabTmaConfig<T, P, NQ, NSTAGE>::THREADS)
           ay[i] = src[i * RL + CUBE];
           az[i] = src[i * RL + 2 * CUBE];
         }
-        T bx[ND], by[ND], bz[ND];
+      }
 #pragma unroll
-        for (int i = 0; i < ND; ++i)
+      for (int i = 0; i < ND; ++i)
+      {
+        bx[i] = 0;
+        by[i] = 0;
+        bz[i] = 0;
+      }
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch, ++slot)
+      {
+        // refill the slot consumed one step ago with the slot NSTAGE-1 ahead in the stream
+        if (lane == 0 && slot + NSTAGE - 1 < total_slots)
+          issue(slot + NSTAGE - 1);
+        const int st = slot % NSTAGE;
+        mbar_wait(bars + st, (slot / NSTAGE) & 1);
+        if (active)
         {
-          bx[i] = 0;
-          by[i] = 0;
-          bz[i] = 0;
-        }
-#pragma unroll
-        for (int q0 = 0; q0 < NQ; ++q0)
-        {
-          const T* g = gs + q0 * (6 * ROW);
-          const T G0 = g[0 * ROW], G1 = g[1 * ROW], G2 = g[2 * ROW];
-          const T G3 = g[3 * ROW], G4 = g[4 * ROW], G5 = g[5 * ROW];
-          T gx = 0, gy, gz;
-          if constexpr (IDENTITY)
-          {
-            gy = ay[q0];
-            gz = az[q0];
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-              gx += tab.dphi[q0 * ND + i] * ax[i];
-          }
+          const T* gs = ring + st * TC::SLOT + rbase + m;
+          // Q0B must be a compile-time constant: dispatch on the unrolled chunk index
+          if constexpr (NCH == 1)
+            slab_z_points<T, ND, NQ, ROW, IDENTITY, 0, Q0C, false>(tab, ax, ay, az, bx, by, bz, gs, kappa);
           else
           {
-            gy = 0;
-            gz = 0;
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-            {
-              gx += tab.dphi[q0 * ND + i] * ax[i];
-              gy += tab.phi[q0 * ND + i] * ay[i];
-              gz += tab.phi[q0 * ND + i] * az[i];
-            }
-          }
-          const T fx = kappa * (G0 * gx + G1 * gy + G2 * gz);
-          const T fy = kappa * (G1 * gx + G3 * gy + G4 * gz);
-          const T fz = kappa * (G2 * gx + G4 * gy + G5 * gz);
-          if constexpr (IDENTITY)
-          {
-            by[q0] = fy;
-            bz[q0] = fz;
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-              bx[i] += tab.dphi[q0 * ND + i] * fx;
-          }
-          else
-          {
-#pragma unroll
-            for (int i = 0; i < ND; ++i)
-            {
-              bx[i] += tab.dphi[q0 * ND + i] * fx;
-              by[i] += tab.phi[q0 * ND + i] * fy;
-              bz[i] += tab.phi[q0 * ND + i] * fz;
-            }
+            if (ch == 0)
+              slab_z_points<T, ND, NQ, ROW, IDENTITY, 0, Q0C, false>(tab, ax, ay, az, bx, by, bz, gs, kappa);
+            if constexpr (NCH > 1)
+              if (ch == 1)
+                slab_z_points<T, ND, NQ, ROW, IDENTITY, (NCH > 1 ? Q0C : 0), Q0C, false>(tab, ax, ay, az, bx,
+                                                                                      by, bz, gs, kappa);
+            if constexpr (NCH > 2)
+              if (ch == 2)
+                slab_z_points<T, ND, NQ, ROW, IDENTITY, (NCH > 2 ? 2 * Q0C : 0), Q0C, false>(
+                    tab, ax, ay, az, bx, by, bz, gs, kappa);
+            if constexpr (NCH > 3)
+              if (ch == 3)
+                slab_z_points<T, ND, NQ, ROW, IDENTITY, (NCH > 3 ? 3 * Q0C : 0), Q0C, false>(
+                    tab, ax, ay, az, bx, by, bz, gs, kappa);
           }
         }
+        __syncwarp(); // every lane is done with slot `st` before it is refilled
+      }
+      if (active)
+      {
 #pragma unroll
         for (int i = 0; i < ND; ++i)
         {
@@ -740,91 +685,53 @@ __global__ void __launch_bounds__(SlabTmaConfig<T, P, NQ, NSTAGE>::THREADS)
           src[i * RL + 2 * CUBE] = bz[i];
         }
       }
-      __syncwarp(); // every lane is done with slot `st` before it is refilled
     }
+    __syncwarp();
 
     // next batch's input values: in flight during the backward phase
-    T nul[ND2];
-    std::int8_t nflag[ND2];
-    load_values(ndof, nul, nflag);
+    T nul[PREFETCH ? ND2 : 1];
+    if constexpr (PREFETCH)
+      load_values(nrow, ndof, nul);
 
-    // ------------------------------------------------------------------ backward X phase + scatter
     if (xlane)
     {
       T out[ND2];
-#pragma unroll
-      for (int t = 0; t < ND2; ++t)
-        out[t] = 0;
-#pragma unroll
-      for (int q2 = 0; q2 < NQ; ++q2)
+      slab_backward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, cube + m * RL + rbase, out);
+      if constexpr (PREFETCH)
       {
-        T e1[ND], e2[ND];
 #pragma unroll
-        for (int j = 0; j < ND; ++j)
+        for (int t = 0; t < ND2; ++t)
+          if (dof[t] >= 0)
+            atomicAdd(y + dof[t], out[t]); // result unused -> RED.E.ADD (reference :424-425)
+      }
+      else
+      {
+#pragma unroll
+        for (int t = 0; t < ND2; ++t)
         {
-          e1[j] = 0;
-          e2[j] = 0;
-        }
-#pragma unroll
-        for (int q1 = 0; q1 < NQ; ++q1)
-        {
-          const T* src = cube + (q1 * ND + m) * RL + rbase + q2;
-          const T bx = src[0], by = src[CUBE], bz = src[2 * CUBE];
-          if constexpr (IDENTITY)
-          {
-            e1[q1] += bx;
-            e2[q1] += bz;
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-              e1[j] += tab.dphi[q1 * ND + j] * by;
-          }
-          else
-          {
-#pragma unroll
-            for (int j = 0; j < ND; ++j)
-            {
-              e1[j] += tab.phi[q1 * ND + j] * bx;
-              e1[j] += tab.dphi[q1 * ND + j] * by;
-              e2[j] += tab.phi[q1 * ND + j] * bz;
-            }
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
-        {
-          if constexpr (IDENTITY)
-          {
-            out[j * ND + q2] += e1[j];
-#pragma unroll
-            for (int kk = 0; kk < ND; ++kk)
-              out[j * ND + kk] += tab.dphi[q2 * ND + kk] * e2[j];
-          }
-          else
-          {
-#pragma unroll
-            for (int kk = 0; kk < ND; ++kk)
-            {
-              out[j * ND + kk] += tab.phi[q2 * ND + kk] * e1[j];
-              out[j * ND + kk] += tab.dphi[q2 * ND + kk] * e2[j];
-            }
-          }
+          const std::int32_t d = row[t]; // re-read (cache hit) instead of holding ND2 registers
+          if (d >= 0)
+            atomicAdd(y + d, out[t]);
         }
       }
-#pragma unroll
-      for (int t = 0; t < ND2; ++t)
-        if (dof[t] >= 0)
-          atomicAdd(y + dof[t], out[t]);
     }
     __syncwarp(); // the cube is rewritten by the next batch's forward phase
-#pragma unroll
-    for (int t = 0; t < ND2; ++t)
+    if constexpr (PREFETCH)
     {
-      dof[t] = ndof[t];
-      ul[t] = nul[t];
-      flag[t] = nflag[t];
+#pragma unroll
+      for (int t = 0; t < ND2; ++t)
+      {
+        dof[t] = ndof[t];
+        ul[t] = nul[t];
+      }
     }
   }
 }
+
+// Masked dofmap: bit 31 of every entry = BC marker of that dof (setup, once per operator).
+__global__ void __launch_bounds__(256)
+    mask_dofmap_kernel(std::int64_t n, const std::int32_t* __restrict__ dofmap,
+                       const std::int8_t* __restrict__ bc, std::int32_t* __restrict__ out);
 
 // Slab layout -> reference layout G[pos][comp][nq^3] (tests / bd_laplacian_geometry only).
 template <typename T>
