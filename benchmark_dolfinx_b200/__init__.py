@@ -33,7 +33,8 @@ from . import _lib
 from ._lib import BenchDolfinxError, check, lib
 
 __all__ = [
-    "BenchDolfinxError", "Tables", "BoxMesh", "Comm", "Halo", "MatFreeLaplacianGPU", "cg_solve",
+    "BenchDolfinxError", "Tables", "BoxMesh", "Comm", "Halo", "MatFreeLaplacianGPU", "MatrixOperator",
+    "cg_solve",
     "axpy", "inner_product", "norm", "set_value", "compute_mesh_size", "partition_grid",
     "laplace_action_gpu", "BenchmarkResults", "device_information",
 ]
@@ -381,6 +382,35 @@ class MatFreeLaplacianGPU:
         return _memcpy_to_host(out, p.value) if out.size else out
 
 
+class MatrixOperator:
+    """Assembled-CSR operator for the --mat_comp check (src/csr.hpp:116-233), assembled on the
+    device from a MatFreeLaplacianGPU's own data; same ``apply(in, out)`` duck type."""
+
+    def __init__(self, op: MatFreeLaplacianGPU):
+        self.value_type, self.bits, self.ndofs, self.n_owned = op.value_type, op.bits, op.ndofs, op.n_owned
+        self.halo = op.halo
+        self._keep = op
+        self._h = C.c_void_p()
+        check(lib.bd_csr_assemble(op._h, int(op.n_owned), C.byref(self._h)))
+        nr, nc, nnz = C.c_int64(), C.c_int64(), C.c_int64()
+        check(lib.bd_csr_info(self._h, C.byref(nr), C.byref(nc), C.byref(nnz)))
+        self.shape, self.nnz = (nr.value, nc.value), nnz.value
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib.bd_csr_destroy(h)
+
+    _check_vec = MatFreeLaplacianGPU._check_vec
+
+    def apply(self, in_, out, stream=None):
+        self._check_vec(in_)
+        self._check_vec(out)
+        if self.halo is not None:
+            self.halo.scatter_fwd(in_, stream)
+        check(lib.bd_csr_apply(self._h, in_.data_ptr(), out.data_ptr(), _stream_ptr(stream)))
+
+
 # ------------------------------------------------------------------ vector functions (src/vector.hpp)
 def axpy(r, alpha, x, y, n=None, stream=None):
     """r = alpha*x + y over the first n (owned) entries (src/vector.hpp:228-240)."""
@@ -412,14 +442,42 @@ def norm(a, n=None, comm: Comm | None = None) -> float:
 
 def cg_solve(A: MatFreeLaplacianGPU, x, b, max_iter: int, rtol: float = 0.0, comm: Comm | None = None,
              stream=None) -> int:
-    """Unpreconditioned CG (src/cg.hpp:89-169); returns the iteration count."""
+    """Unpreconditioned CG (src/cg.hpp:89-169); returns the iteration count.  For the matrix-free
+    operator the whole solve is the fused device loop of bd_cg_solve; any other duck-typed operator
+    (the CSR check operator) runs the same recurrence through the vector functions."""
     A._check_vec(x)
     A._check_vec(b)
+    if not isinstance(A, MatFreeLaplacianGPU):
+        return _cg_solve_generic(A, x, b, max_iter, rtol, comm)
     its = C.c_int(0)
     halo = A.halo._h if A.halo is not None else None
     check(lib.bd_cg_solve(A._h, halo, comm._h if comm is not None else None, x.data_ptr(), b.data_ptr(),
                           int(max_iter), float(rtol), C.byref(its), _stream_ptr(stream)))
     return its.value
+
+
+def _cg_solve_generic(A, x, b, max_iter, rtol, comm):
+    import torch
+    n = A.n_owned
+    y, r, p = torch.zeros_like(x), torch.zeros_like(x), torch.zeros_like(x)
+    A.apply(x, y)
+    axpy(r, -1.0, y, b, n)
+    axpy(p, 0.0, r, r, n)
+    rnorm0 = rnorm = inner_product(p, r, n, comm)
+    k = 0
+    while k < max_iter:
+        k += 1
+        A.apply(p, y)
+        alpha = rnorm / inner_product(p, y, n, comm)
+        axpy(x, alpha, p, x, n)
+        axpy(r, -alpha, y, r, n)
+        rnorm_new = inner_product(r, r, n, comm)
+        beta = rnorm_new / rnorm
+        rnorm = rnorm_new
+        if rnorm / rnorm0 < rtol * rtol:
+            break
+        axpy(p, beta, p, r, n)
+    return k
 
 
 # ------------------------------------------------------------------ benchmark harness
@@ -434,7 +492,7 @@ class BenchmarkResults:
 
 
 def laplace_action_gpu(mesh: BoxMesh, degree, qmode, kappa, nreps, use_gauss=False, use_cg=False,
-                       comm: Comm | None = None, dtype=np.float64, verbose=False):
+                       comm: Comm | None = None, dtype=np.float64, verbose=False, matrix_comparison=False):
     """The timed benchmark body of the reference (src/laplacian_solver.cpp:66-149): build the
     operator, u := assembled RHS, then ``nreps`` operator applications or ``nreps`` CG iterations,
     wall-clocked, followed by the norms of u and y."""
@@ -463,4 +521,21 @@ def laplace_action_gpu(mesh: BoxMesh, degree, qmode, kappa, nreps, use_gauss=Fal
         print(f"Computation rate (Gdofs/s): {mesh.ndofs_global * nreps / (1e9 * res.mat_free_time)}")
         print(f"Norm of u = {res.unorm}")
         print(f"Norm of y = {res.ynorm}")
+    if matrix_comparison:                                        # src/laplacian_solver.cpp:151-227
+        mat_op = MatrixOperator(op)
+        z = torch.zeros_like(u)
+        if use_cg:
+            cg_solve(mat_op, z, u, nreps, 0.0, comm)
+        else:
+            for _ in range(nreps):
+                mat_op.apply(u, z)
+        e = torch.zeros_like(u)
+        axpy(e, -1.0, y, z, mesh.ndofs_owned)
+        res.znorm = norm(z, mesh.ndofs_owned, comm)
+        res.enorm = norm(e, mesh.ndofs_owned, comm)
+        if verbose and (comm is None or comm.rank == 0):
+            print(f"Norm of u = {res.unorm}")
+            print(f"Norm of z = {res.znorm}")
+            print(f"Norm of error = {res.enorm}")
+            print(f"Relative norm of error = {res.enorm / res.znorm}")
     return res, op, u, y

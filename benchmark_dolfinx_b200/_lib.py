@@ -101,6 +101,10 @@ PROTOTYPES = {
     "bd_cg_solve": (C.c_int, [_V, _V, _V, _V, _V, C.c_int, C.c_double, C.POINTER(C.c_int), _V]),
     "bd_inner_product": (C.c_int, [_V, C.c_int, C.c_int64, _V, _V, C.POINTER(C.c_double)]),
     "bd_norm": (C.c_int, [_V, C.c_int, C.c_int64, _V, C.POINTER(C.c_double)]),
+    "bd_csr_assemble": (C.c_int, [_V, C.c_int64, C.POINTER(_V)]),
+    "bd_csr_destroy": (C.c_int, [_V]),
+    "bd_csr_info": (C.c_int, [_V, c_i64p, c_i64p, c_i64p]),
+    "bd_csr_apply": (C.c_int, [_V, _V, _V, _V]),
     "bd_compute_mesh_size": (C.c_int, [C.c_int64, C.c_int, c_i64p]),
     "bd_boxmesh_create": (C.c_int, [C.c_int, c_i64p, C.c_int, C.c_int, C.c_int, c_i32p, C.c_double,
                                     C.POINTER(_V)]),

@@ -229,6 +229,21 @@ int bd_inner_product(bd_comm* comm, int scalar_bits, int64_t n_owned, const void
 int bd_norm(bd_comm* comm, int scalar_bits, int64_t n_owned, const void* a, double* result_host);
 
 /* ------------------------------------------------------------------------- *
+ * Assembled-CSR check path (--mat_comp): replaces MatrixOperator<T> (src/csr.hpp:116-233) and the
+ * CPU assembly that feeds it (src/laplacian_solver.cpp:160-191).  The matrix is assembled on the
+ * device from the operator's own mesh data and geometry tensor, without sum factorisation: BC rows
+ * and columns dropped, unit diagonal on BC rows, owned rows only (n_owned of them).
+ * A correctness check, not a performance path.
+ * ------------------------------------------------------------------------- */
+typedef struct bd_csr bd_csr;
+int bd_csr_assemble(bd_laplacian* op, int64_t n_owned, bd_csr** out);
+int bd_csr_destroy(bd_csr* A);
+int bd_csr_info(bd_csr* A, int64_t* nrows, int64_t* ncols, int64_t* nnz);
+/* out = A in  (MatrixOperator::apply, src/csr.hpp:174-217): zero `out` (owned + ghost), then the
+ * owned rows; `in` needs current ghost values. */
+int bd_csr_apply(bd_csr* A, const void* in_dev, void* out_dev, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Stand-in for the DOLFINx host setup (mesh, dofmap, BCs, RHS), generated on the
  * device for one rank of a block partition of the compute_mesh_size box
  * (src/mesh.cpp:117-152,190-218; src/main.cpp:54-102; src/laplacian_solver.cpp:100-109).
