@@ -328,7 +328,7 @@ def main():
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
-        "kernel": f"bd::stiffness_kernel<{'double' if args.float == 64 else 'float'},{degree},{nq}>",
+        "kernel": op.describe(),
         "kernel_ms_per_apply": 1e3 * kernel_s_per_apply, "kernel_launches_per_apply": launches_per_apply,
         "algorithmic_bytes_per_apply": bytes_apply,
         "algorithmic_bytes_per_dof": bytes_apply / mesh.ndofs_local,

@@ -363,6 +363,11 @@ class MatFreeLaplacianGPU:
         halo = self.halo._h if self.halo is not None else None
         check(lib.bd_laplacian_apply_host(self._h, halo, _ptr(in_host), _ptr(out_host)))
 
+    def describe(self) -> str:
+        buf = C.create_string_buffer(256)
+        check(lib.bd_laplacian_describe(self._h, buf, 256))
+        return buf.value.decode()
+
     def profile(self, enable: bool):
         """Bracket every stiffness-kernel launch with CUDA events (roofline measurement)."""
         check(lib.bd_laplacian_profile(self._h, int(enable)))

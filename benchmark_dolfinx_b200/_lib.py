@@ -76,6 +76,7 @@ PROTOTYPES = {
     "bd_laplacian_apply_part": (C.c_int, [_V, C.c_int, _V, _V, _V]),
     "bd_laplacian_apply_host": (C.c_int, [_V, _V, _V, _V]),
     "bd_laplacian_profile": (C.c_int, [_V, C.c_int]),
+    "bd_laplacian_describe": (C.c_int, [_V, C.c_char_p, C.c_size_t]),
     "bd_laplacian_profile_read": (C.c_int, [_V, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "bd_laplacian_geometry": (C.c_int, [_V, C.POINTER(_V), C.POINTER(C.c_int64)]),
     "bd_geometry_compute": (C.c_int, [C.c_int, C.c_int, _V, _V, _V, _V, _V, C.c_int64, _V, _V]),

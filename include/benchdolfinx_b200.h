@@ -110,6 +110,8 @@ int bd_laplacian_apply_host(bd_laplacian* op, struct bd_halo* halo, const void* 
  * and the number of launches since the last read, and resets the counters.  (The reference only
  * has dolfinx::common::Timer scopes around whole phases, src/laplacian_solver.cpp:90,197.) */
 int bd_laplacian_profile(bd_laplacian* op, int enable);
+/* One-line description of the stiffness kernel variant this operator launches (for reports). */
+int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n);
 int bd_laplacian_profile_read(bd_laplacian* op, double* total_ms, int64_t* launches);
 
 /* Read-only access to the precomputed geometry tensor, device pointer to
