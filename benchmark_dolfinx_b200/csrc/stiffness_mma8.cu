@@ -2,9 +2,11 @@
 #include "stiffness_launch.cuh"
 #include "stiffness_mma8.cuh"
 
+#include <cstdlib>
+
 namespace bd
 {
-template <int P, bool IDENTITY>
+template <int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 static int launch_mma8(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
@@ -14,7 +16,7 @@ static int launch_mma8(const StiffnessArgs& a)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap)
     return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA kernel needs the masked dofmap");
-  auto kernel = stiffness_mma8_kernel<P, IDENTITY>;
+  auto kernel = stiffness_mma8_kernel<P, IDENTITY, kMma8Warps, PREFETCH>;
   constexpr int smem = kMma8Warps * kMma8WarpSmem;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
@@ -47,12 +49,28 @@ static int launch_mma8(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
+static int env_int(const char* name, int dflt)
+{
+  const char* e = std::getenv(name);
+  return e ? std::atoi(e) : dflt;
+}
+
+template <int P, bool IDENTITY>
+static int launch_mma8_tuned(const StiffnessArgs& a)
+{
+  // tuning knobs for experiments: BD_MMA8_WARPS (2|4 warps per CTA), BD_MMA8_PREFETCH (0|1)
+  static const int warps = env_int("BD_MMA8_WARPS", 4), prefetch = env_int("BD_MMA8_PREFETCH", 1);
+  if (warps == 4)
+    return prefetch ? launch_mma8<P, IDENTITY, 4, true>(a) : launch_mma8<P, IDENTITY, 4, false>(a);
+  return prefetch ? launch_mma8<P, IDENTITY, 2, true>(a) : launch_mma8<P, IDENTITY, 2, false>(a);
+}
+
 int launch_stiffness_mma8(int degree, bool identity, const StiffnessArgs& a)
 {
   if (degree == 6 && !identity)
-    return launch_mma8<6, false>(a);
+    return launch_mma8_tuned<6, false>(a);
   if (degree == 7 && identity)
-    return launch_mma8<7, true>(a);
+    return launch_mma8_tuned<7, true>(a);
   return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers degree 6 / qmode 1 and degree 7 / qmode 0 only");
 }
 } // namespace bd

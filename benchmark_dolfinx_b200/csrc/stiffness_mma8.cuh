@@ -37,7 +37,6 @@ struct Mma8Tables
 constexpr int kMma8Stages = 4;
 constexpr int kMma8SlotBytes = 6 * 2 * 32 * 8; // one y-tile of G: 6 components x 2 registers x 32 lanes
 constexpr int kMma8WarpSmem = kMma8Stages * kMma8SlotBytes + 64;
-constexpr int kMma8Warps = 4;
 constexpr std::int64_t kMma8CellG = 8 * 6 * 2 * 32; // doubles of G per cell
 
 // Position of (cell pos, comp, q0, q1, q2) in the accumulator-order G layout.
@@ -97,7 +96,7 @@ __device__ __forceinline__ void mma8_tile(const double (&M)[64], const double (&
   }
 }
 
-template <int P, bool IDENTITY>
+template <int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 __global__ void __launch_bounds__(kMma8Warps * 32)
     stiffness_mma8_kernel(const double* __restrict__ u, double* __restrict__ y, const double* __restrict__ Gf,
                           const double* __restrict__ cell_constants,
@@ -161,15 +160,43 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
     for (int s = 0; s < NSTAGE - 1 && s < total_slots; ++s)
       issue(s);
 
+  // dof indices of lane (g, t): (x = g, y, z = 2t + s); entries outside the ND^3 dofs look like
+  // constrained dofs that are never touched
+  auto load_dofs = [&](int cell_pos, std::int32_t (&d)[8][2]) {
+    const std::int32_t* row = mdofmap + static_cast<std::int64_t>(cells[cell_pos]) * ND3;
+#pragma unroll
+    for (int yy = 0; yy < 8; ++yy)
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+      {
+        const int z = 2 * t + s;
+        const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
+        d[yy][s] = valid ? row[(g * ND + yy) * ND + z] : kBcBit;
+      }
+  };
+  std::int32_t dof[8][2], ndof[8][2];
+  if (PREFETCH && my_cells > 0)
+    load_dofs(first, ndof);
+
   int slot = 0;
   for (int k = 0; k < my_cells; ++k)
   {
     const int pos = first + k * warps_total;
-    const std::int32_t* row = mdofmap + static_cast<std::int64_t>(cells[pos]) * ND3;
 
     // ---- gather: T[x = g][y][z = 2t + s], zero outside the ND^3 dofs and on constrained dofs
-    std::int32_t dof[8][2];
     double T[8][2];
+    if constexpr (PREFETCH)
+    {
+#pragma unroll
+      for (int yy = 0; yy < 8; ++yy)
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+          dof[yy][s] = ndof[yy][s];
+    }
+    else
+      load_dofs(pos, dof);
+    // all 16 loads are issued before the first use (a store placed between them would serialise the
+    // round trips: the warp stalls in order on the store's operands)
 #pragma unroll
     for (int yy = 0; yy < 8; ++yy)
 #pragma unroll
@@ -177,8 +204,11 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       {
         const int z = 2 * t + s;
         const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
-        dof[yy][s] = valid ? row[(g * ND + yy) * ND + z] : kBcBit;
+        T[yy][s] = valid ? u[dof[yy][s] & 0x7fffffff] : 0.0;
       }
+    // the next cell's indices travel while this cell is computed
+    if (PREFETCH && k + 1 < my_cells)
+      load_dofs(pos + warps_total, ndof);
 #pragma unroll
     for (int yy = 0; yy < 8; ++yy)
 #pragma unroll
@@ -186,17 +216,11 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       {
         const int z = 2 * t + s;
         const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
-        double v = 0;
-        if (valid)
+        if (valid && dof[yy][s] < 0)
         {
-          v = u[dof[yy][s] & 0x7fffffff];
-          if (dof[yy][s] < 0)
-          {
-            y[dof[yy][s] & 0x7fffffff] = v; // b[dof] = u[dof] on constrained dofs (reference :163-166)
-            v = 0;
-          }
+          y[dof[yy][s] & 0x7fffffff] = T[yy][s]; // b[dof] = u[dof] on constrained dofs (reference :163-166)
+          T[yy][s] = 0;
         }
-        T[yy][s] = v;
       }
 
     // ---- interpolation to the quadrature points (reference :175-211)
