@@ -162,8 +162,8 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
 
   // dof indices of lane (g, t): (x = g, y, z = 2t + s); entries outside the ND^3 dofs look like
   // constrained dofs that are never touched
-  auto load_dofs = [&](int cell_pos, std::int32_t (&d)[8][2]) {
-    const std::int32_t* row = mdofmap + static_cast<std::int64_t>(cells[cell_pos]) * ND3;
+  auto load_dofs = [&](std::int32_t cell, std::int32_t (&d)[8][2]) {
+    const std::int32_t* row = mdofmap + static_cast<std::int64_t>(cell) * ND3;
 #pragma unroll
     for (int yy = 0; yy < 8; ++yy)
 #pragma unroll
@@ -175,13 +175,19 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       }
   };
   std::int32_t dof[8][2], ndof[8][2];
+  // cell index and kappa are loaded one / two cells ahead (first-use stalls otherwise)
+  std::int32_t cell_cur = my_cells > 0 ? cells[first] : 0;
+  std::int32_t cell_next = my_cells > 1 ? cells[first + warps_total] : 0;
+  double kappa = my_cells > 0 ? cell_constants[first] : 0.0;
   if (PREFETCH && my_cells > 0)
-    load_dofs(first, ndof);
+    load_dofs(cell_cur, ndof);
 
   int slot = 0;
   for (int k = 0; k < my_cells; ++k)
   {
     const int pos = first + k * warps_total;
+    const std::int32_t cell_next2 = k + 2 < my_cells ? cells[pos + 2 * warps_total] : 0;
+    const double kappa_next = k + 1 < my_cells ? cell_constants[pos + warps_total] : 0.0;
 
     // ---- gather: T[x = g][y][z = 2t + s], zero outside the ND^3 dofs and on constrained dofs
     double T[8][2];
@@ -194,7 +200,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
           dof[yy][s] = ndof[yy][s];
     }
     else
-      load_dofs(pos, dof);
+      load_dofs(cell_cur, dof);
     // all 16 loads are issued before the first use (a store placed between them would serialise the
     // round trips: the warp stalls in order on the store's operands)
 #pragma unroll
@@ -208,7 +214,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       }
     // the next cell's indices travel while this cell is computed
     if (PREFETCH && k + 1 < my_cells)
-      load_dofs(pos + warps_total, ndof);
+      load_dofs(cell_next, ndof);
 #pragma unroll
     for (int yy = 0; yy < 8; ++yy)
 #pragma unroll
@@ -245,7 +251,6 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
     double F[8][2]; // g_y, then f_y
     mma8_tile<false, false>(tab.dphi, T, F);
     double R[8][2];
-    const double kappa = cell_constants[pos];
 #pragma unroll
     for (int yy = 0; yy < 8; ++yy, ++slot)
     {
@@ -302,6 +307,9 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       for (int s = 0; s < 2; ++s)
         if (dof[yy][s] >= 0)
           atomicAdd(y + dof[yy][s], R[yy][s]);
+    cell_cur = cell_next;
+    cell_next = cell_next2;
+    kappa = kappa_next;
   }
 }
 

@@ -556,10 +556,19 @@ __global__ void __launch_bounds__(WARPS_ * 32)
       issue(s);
   }
 
-  auto row_of = [&](int batch) -> const std::int32_t* {
+  // Cell index and kappa of a batch are loaded a whole batch ahead: ncu showed the warp stalling in
+  // order on cells[pos] (address of the dof row) and on cell_constants[pos] right at their first use.
+  auto cell_of = [&](int batch) -> std::int32_t {
     const int pos = batch * CW + c;
     const bool x = lane_ok && batch < nbatches && pos < ncells && m < ND;
-    return x ? mdofmap + static_cast<std::int64_t>(cells[pos]) * ND3 + m * ND2 : nullptr;
+    return x ? cells[pos] : -1;
+  };
+  auto kappa_of = [&](int batch) -> T {
+    const int pos = batch * CW + c;
+    return (lane_ok && batch < nbatches && pos < ncells) ? cell_constants[pos] : T(0);
+  };
+  auto row_from = [&](std::int32_t cell) -> const std::int32_t* {
+    return cell >= 0 ? mdofmap + static_cast<std::int64_t>(cell) * ND3 + m * ND2 : nullptr;
   };
   auto load_dofs = [&](const std::int32_t* row, std::int32_t (&d)[ND2]) {
 #pragma unroll
@@ -574,9 +583,12 @@ __global__ void __launch_bounds__(WARPS_ * 32)
 
   std::int32_t dof[ND2];
   T ul[ND2];
+  std::int32_t cell_cur = my_batches > 0 ? cell_of(first) : -1;
+  std::int32_t cell_next = my_batches > 1 ? cell_of(first + warps_total) : -1;
+  T kappa = my_batches > 0 ? kappa_of(first) : T(0);
   if constexpr (PREFETCH)
   {
-    const std::int32_t* row = row_of(first);
+    const std::int32_t* row = row_from(cell_cur);
     load_dofs(row, dof);
     load_values(row, dof, ul);
   }
@@ -588,7 +600,10 @@ __global__ void __launch_bounds__(WARPS_ * 32)
     const int pos = batch * CW + c;
     const bool active = lane_ok && pos < ncells;
     const bool xlane = active && m < ND;
-    const std::int32_t* row = row_of(batch);
+    const std::int32_t* row = row_from(cell_cur);
+    // two batches ahead / one batch ahead: consumed at the end of this iteration
+    const std::int32_t cell_next2 = k + 2 < my_batches ? cell_of(batch + 2 * warps_total) : -1;
+    const T kappa_next = k + 1 < my_batches ? kappa_of(batch + warps_total) : T(0);
 
     if constexpr (!PREFETCH)
     {
@@ -614,11 +629,10 @@ __global__ void __launch_bounds__(WARPS_ * 32)
     const std::int32_t* nrow = nullptr;
     if constexpr (PREFETCH)
     {
-      nrow = row_of(batch + warps_total);
+      nrow = row_from(cell_next);
       load_dofs(nrow, ndof);
     }
 
-    const T kappa = active ? cell_constants[pos] : T(0);
 #pragma unroll 1
     for (int q1 = 0; q1 < NQ; ++q1)
     {
@@ -725,6 +739,9 @@ __global__ void __launch_bounds__(WARPS_ * 32)
         ul[t] = nul[t];
       }
     }
+    cell_cur = cell_next;
+    cell_next = cell_next2;
+    kappa = kappa_next;
   }
 }
 
