@@ -363,6 +363,18 @@ class MatFreeLaplacianGPU:
         halo = self.halo._h if self.halo is not None else None
         check(lib.bd_laplacian_apply_host(self._h, halo, _ptr(in_host), _ptr(out_host)))
 
+    def apply_host_batch(self, ins, outs):
+        """outs[i] = A ins[i] for lists of host vectors; copies and operator are pipelined."""
+        n = len(ins)
+        assert n == len(outs)
+        for a, b in zip(ins, outs):
+            assert a.dtype == self.value_type and b.dtype == self.value_type
+            assert a.size == self.ndofs and b.size == self.ndofs
+        pin = (C.c_void_p * n)(*[_ptr(a) for a in ins])
+        pout = (C.c_void_p * n)(*[_ptr(b) for b in outs])
+        halo = self.halo._h if self.halo is not None else None
+        check(lib.bd_laplacian_apply_host_batch(self._h, halo, n, pin, pout))
+
     def describe(self) -> str:
         buf = C.create_string_buffer(256)
         check(lib.bd_laplacian_describe(self._h, buf, 256))

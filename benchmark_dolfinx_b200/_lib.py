@@ -75,6 +75,7 @@ PROTOTYPES = {
     "bd_laplacian_apply": (C.c_int, [_V, _V, _V, _V]),
     "bd_laplacian_apply_part": (C.c_int, [_V, C.c_int, _V, _V, _V]),
     "bd_laplacian_apply_host": (C.c_int, [_V, _V, _V, _V]),
+    "bd_laplacian_apply_host_batch": (C.c_int, [_V, _V, C.c_int, _V, _V]),
     "bd_laplacian_profile": (C.c_int, [_V, C.c_int]),
     "bd_laplacian_describe": (C.c_int, [_V, C.c_char_p, C.c_size_t]),
     "bd_laplacian_profile_read": (C.c_int, [_V, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),

@@ -144,8 +144,16 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
 extern "C" int bd_laplacian_destroy(bd_laplacian* op)
 {
   if (op)
+  {
     for (cudaEvent_t e : op->prof_events)
       cudaEventDestroy(e);
+    for (cudaEvent_t e : op->batch_events)
+      if (e)
+        cudaEventDestroy(e);
+    for (cudaStream_t st : op->batch_streams)
+      if (st)
+        cudaStreamDestroy(st);
+  }
   delete op;
   return BD_SUCCESS;
 }
@@ -282,5 +290,61 @@ extern "C" int bd_laplacian_apply_host(bd_laplacian* op, bd_halo* halo, const vo
   BD_CHECK(bd_laplacian_apply_halo(op, halo, op->stage_in.ptr, op->stage_out.ptr, nullptr));
   BD_CUDA_CHECK(cudaMemcpyAsync(out_host, op->stage_out.ptr, bytes, cudaMemcpyDeviceToHost, nullptr));
   BD_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+  return BD_SUCCESS;
+}
+
+// Pipelined host-vector entry point: H2D of vector i+1, the operator on vector i and D2H of vector
+// i-1 run concurrently on three streams with two staging pairs, so a sequence of host vectors costs
+// max(H2D, apply, D2H) per vector instead of their sum (PCIe is full duplex).
+extern "C" int bd_laplacian_apply_host_batch(bd_laplacian* op, bd_halo* halo, int nvec,
+                                             const void* const* in_host, void* const* out_host)
+{
+  BD_REQUIRE(op && nvec >= 0, "bd_laplacian_apply_host_batch: bad argument");
+  if (nvec == 0)
+    return BD_SUCCESS;
+  BD_REQUIRE(in_host && out_host, "bd_laplacian_apply_host_batch: null argument");
+  const size_t bytes = static_cast<size_t>(op->ndofs) * op->scalar_size();
+  if (op->stage_in.count != bytes)
+  {
+    BD_CHECK(op->stage_in.alloc(bytes));
+    BD_CHECK(op->stage_out.alloc(bytes));
+  }
+  if (op->stage_in2.count != bytes)
+  {
+    BD_CHECK(op->stage_in2.alloc(bytes));
+    BD_CHECK(op->stage_out2.alloc(bytes));
+  }
+  if (!op->batch_streams[0])
+  {
+    for (auto& st : op->batch_streams)
+      BD_CUDA_CHECK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto& ev : op->batch_events)
+      BD_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  }
+  cudaStream_t h2d = op->batch_streams[0], comp = op->batch_streams[1], d2h = op->batch_streams[2];
+  char* sin[2] = {op->stage_in.ptr, op->stage_in2.ptr};
+  char* sout[2] = {op->stage_out.ptr, op->stage_out2.ptr};
+  cudaEvent_t* ev_in = op->batch_events;       // [2] input staged
+  cudaEvent_t* ev_done = op->batch_events + 2; // [2] operator finished (input slot free, output ready)
+  cudaEvent_t* ev_out = op->batch_events + 4;  // [2] output copied (output slot free)
+  for (int i = 0; i < nvec; ++i)
+  {
+    const int s = i & 1;
+    BD_REQUIRE(in_host[i] && out_host[i], "bd_laplacian_apply_host_batch: null vector %d", i);
+    if (i >= 2)
+      BD_CUDA_CHECK(cudaStreamWaitEvent(h2d, ev_done[s], 0));
+    BD_CUDA_CHECK(cudaMemcpyAsync(sin[s], in_host[i], bytes, cudaMemcpyHostToDevice, h2d));
+    BD_CUDA_CHECK(cudaEventRecord(ev_in[s], h2d));
+    BD_CUDA_CHECK(cudaStreamWaitEvent(comp, ev_in[s], 0));
+    if (i >= 2)
+      BD_CUDA_CHECK(cudaStreamWaitEvent(comp, ev_out[s], 0));
+    BD_CHECK(bd_laplacian_apply_halo(op, halo, sin[s], sout[s], comp));
+    BD_CUDA_CHECK(cudaEventRecord(ev_done[s], comp));
+    BD_CUDA_CHECK(cudaStreamWaitEvent(d2h, ev_done[s], 0));
+    BD_CUDA_CHECK(cudaMemcpyAsync(out_host[i], sout[s], bytes, cudaMemcpyDeviceToHost, d2h));
+    BD_CUDA_CHECK(cudaEventRecord(ev_out[s], d2h));
+  }
+  BD_CUDA_CHECK(cudaStreamSynchronize(d2h));
+  BD_CUDA_CHECK(cudaStreamSynchronize(comp));
   return BD_SUCCESS;
 }

@@ -22,6 +22,10 @@ struct bd_laplacian
   std::vector<char> phi0, dphi1;
   // staging for bd_laplacian_apply_host
   bd::DeviceArray<char> stage_in, stage_out;
+  // second staging pair + streams/events of the pipelined bd_laplacian_apply_host_batch
+  bd::DeviceArray<char> stage_in2, stage_out2;
+  cudaStream_t batch_streams[3] = {nullptr, nullptr, nullptr}; // h2d, compute, d2h
+  cudaEvent_t batch_events[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   // optional per-launch timing of the stiffness kernels (bd_laplacian_profile)
   bool profile = false;
   std::vector<cudaEvent_t> prof_events; // pairs (start, stop), consumed by bd_laplacian_profile_read

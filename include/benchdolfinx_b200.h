@@ -104,6 +104,12 @@ struct bd_halo;
 int bd_laplacian_apply_host(bd_laplacian* op, struct bd_halo* halo, const void* in_host,
                             void* out_host);
 
+/* The same for a sequence of host vectors (e.g. several right-hand sides), pipelined: the H2D copy
+ * of vector i+1, the operator on vector i and the D2H copy of vector i-1 overlap on three streams
+ * with two device staging pairs.  out_host[i] = A in_host[i]; synchronous on return. */
+int bd_laplacian_apply_host_batch(bd_laplacian* op, struct bd_halo* halo, int nvec,
+                                  const void* const* in_host, void* const* out_host);
+
 /* Per-launch device timing of the stiffness kernels, for the roofline report: while enabled,
  * every kernel launch of bd_laplacian_apply* is bracketed by CUDA events on the launching stream
  * (no synchronisation); bd_laplacian_profile_read waits for them, returns the summed kernel time

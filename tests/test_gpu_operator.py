@@ -61,3 +61,20 @@ def test_reference_goldens():
         assert abs(bd.norm(yd) - ynorm) / ynorm < 1e-12
         if unorm is not None:
             assert abs(bd.norm(ud) - unorm) / unorm < 1e-12
+
+
+def test_host_batch_entry_point_matches_single_calls():
+    """bd_laplacian_apply_host_batch (pipelined copies) == bd_laplacian_apply_host, vector by vector."""
+    import benchmark_dolfinx_b200 as bd
+    degree, qmode = 3, 1
+    mesh = create_box_mesh(compute_mesh_size(30000, degree), degree, geom_perturb_fact=0.2)
+    op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0)
+    rng = np.random.default_rng(5)
+    ins = [rng.uniform(-1, 1, mesh.ndofs_local) for _ in range(5)]
+    outs = [np.zeros(mesh.ndofs_local) for _ in range(5)]
+    op.apply_host_batch(ins, outs)
+    for a, b in zip(ins, outs):
+        ref = np.zeros_like(a)
+        op.apply_host(a, ref)
+        assert _rel(b, ref) < 1e-14
+    op.apply_host_batch([], [])
