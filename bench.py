@@ -226,6 +226,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--degree", type=int, default=3)
     ap.add_argument("--ndofs", type=int, default=300_000_000, help="dofs per GPU (reference --ndofs)")
+    ap.add_argument("--ndofs_global", type=int, default=0,
+                    help="fixed global size (strong scaling, reference --ndofs_global); overrides --ndofs")
     ap.add_argument("--float", type=int, default=64, choices=[32, 64])
     ap.add_argument("--qmode", type=int, default=1, choices=[0, 1])
     ap.add_argument("--no-cg", action="store_true", help="skip the CG leg")
@@ -276,7 +278,9 @@ def main():
     dtype = np.float64 if args.float == 64 else np.float32
     tsize = args.float // 8
     degree, qmode = args.degree, args.qmode
-    n = bd.compute_mesh_size(args.ndofs * world, degree)           # src/main.cpp:237-238,272-273
+    if args.ndofs_global:                                          # src/main.cpp:237-240
+        args.ndofs = args.ndofs_global // world
+    n = bd.compute_mesh_size(args.ndofs_global or args.ndofs * world, degree)   # src/main.cpp:272-273
     t_setup = time.perf_counter()
     mesh = bd.BoxMesh(n, degree, rank, world, dtype=dtype)
     halo = bd.Halo(comm, mesh) if world > 1 else None
@@ -410,9 +414,10 @@ def main():
         line = {
             "metric": "gdof_per_second_laplacian_action", "value": value, "unit": "GDoF/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True,
+            "scaling": "strong" if args.ndofs_global else "weak",
             "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic",
-            "config": dict(workload_config(args, world), mesh_cells=n, ndofs_global=ndofs_global,
+            "config": dict(workload_config(args, world), ndofs_global_requested=args.ndofs_global or None, mesh_cells=n, ndofs_global=ndofs_global,
                            ncells_global=mesh.ncells_global, setup_seconds=t_setup),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cg": cg,
             "gpu_launches": gpu_launches, "clocks": clocks,

@@ -140,21 +140,6 @@ int geometry_compute_layout(int scalar_bits, int nq, const void* xgeom, const st
              : launch_geometry<float>(nq, xgeom, gdofmap, dphi, weights, cells, ncells, G, stream, layout);
 }
 
-__global__ void __launch_bounds__(256)
-    mma8_g_to_reference_kernel(const double* __restrict__ Gf, double* __restrict__ G, std::int64_t ncells)
-{
-  const std::int64_t total = ncells * 6 * 512;
-  const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
-  for (std::int64_t idx = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
-       idx += stride)
-  {
-    const std::int64_t pos = idx / 3072;
-    const int rem = static_cast<int>(idx - pos * 3072);
-    const int comp = rem / 512, q = rem % 512;
-    G[idx] = Gf[mma8_g_index(pos, comp, q / 64, (q / 8) % 8, q % 8)];
-  }
-}
-
 int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
                           cudaStream_t stream, int layout)
 {
@@ -163,8 +148,12 @@ int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std:
   const int grid = sm_count() * 8;
   if (layout == 2)
   {
-    mma8_g_to_reference_kernel<<<grid, 256, 0, stream>>>(static_cast<const double*>(Gs),
-                                                         static_cast<double*>(G), ncells);
+    if (scalar_bits == 64)
+      mma8_g_to_reference_kernel<double><<<grid, 256, 0, stream>>>(static_cast<const double*>(Gs),
+                                                                  static_cast<double*>(G), ncells);
+    else
+      mma8_g_to_reference_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(Gs),
+                                                                 static_cast<float*>(G), ncells);
     BD_CUDA_CHECK(cudaGetLastError());
     return BD_SUCCESS;
   }

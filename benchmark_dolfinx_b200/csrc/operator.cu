@@ -238,7 +238,7 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
 {
   BD_REQUIRE(op && buf && n > 0, "bd_laplacian_describe: null argument");
   const char* t = op->scalar_bits == 64 ? "double" : "float";
-  const char* kernel = op->g_layout == 2 ? "bd::stiffness_mma8_kernel (fp64 DMMA m8n8k4, UBLKCP G ring)"
+  const char* kernel = op->g_layout == 2 ? "bd::stiffness_mma8_kernel (fp64 DMMA m8n8k4 arithmetic, UBLKCP G ring)"
                        : (stiffness_variant() == 1 ? "bd::stiffness_slab_kernel (register slabs, LDG G)"
                                                    : "bd::stiffness_slab_tma_kernel (register slabs, UBLKCP G ring)");
   snprintf(buf, n, "%s, T=%s, P=%d, nq=%d, G layout %d", kernel, t, op->degree, op->nq, op->g_layout);

@@ -47,7 +47,7 @@ int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::i
 
 int preferred_g_layout(int scalar_bits, int nq)
 {
-  if (scalar_bits == 64 && nq == 8 && stiffness_variant() != 1)
+  if (nq == 8 && stiffness_variant() != 1)
     return 2;
   return 1;
 }
@@ -65,9 +65,9 @@ int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const
 {
   if (a.g_layout == 2)
   {
-    if (scalar_bits != 64 || nq != 8)
-      return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA layout needs fp64 and nq = 8");
-    return launch_stiffness_mma8(degree, identity, a);
+    if (nq != 8)
+      return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA layout needs nq = 8");
+    return launch_stiffness_mma8(scalar_bits, degree, identity, a);
   }
   if (scalar_bits != 32 && scalar_bits != 64)
     return fail(BD_ERR_INVALID_ARGUMENT, "Invalid float size. Must be 32 or 64.");

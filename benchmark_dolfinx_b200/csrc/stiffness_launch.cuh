@@ -206,7 +206,7 @@ int launch_stiffness_f32_q1(int degree, const StiffnessArgs& a);
 
 // in geometry.cu
 // G layouts: 0 = reference [cell][6][nq^3], 1 = slab (stiffness_slab.cuh), 2 = DMMA accumulator
-// order (stiffness_mma8.cuh; nq = 8, fp64 only)
+// order (stiffness_mma8.cuh; nq = 8)
 int geometry_compute_layout(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
                             const void* dphi, const void* weights, const std::int32_t* cells,
                             std::int64_t ncells, void* G, cudaStream_t stream, int layout);
@@ -216,7 +216,7 @@ int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std:
 int preferred_g_layout(int scalar_bits, int nq);
 std::int64_t g_layout_size(int layout, int nq, std::int64_t ncells);
 // in stiffness_mma8.cu
-int launch_stiffness_mma8(int degree, bool identity, const StiffnessArgs& a);
+int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const StiffnessArgs& a);
 // in stiffness.cu: out[i] = dofmap[i] | (bc[dofmap[i]] ? 0x80000000 : 0)
 int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::int8_t* bc,
                         std::int32_t* out, cudaStream_t stream);

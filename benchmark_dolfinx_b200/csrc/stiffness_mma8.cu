@@ -6,7 +6,7 @@
 
 namespace bd
 {
-template <int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
+template <typename TS, int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 static int launch_mma8(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
@@ -16,8 +16,8 @@ static int launch_mma8(const StiffnessArgs& a)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap)
     return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA kernel needs the masked dofmap");
-  auto kernel = stiffness_mma8_kernel<P, IDENTITY, kMma8Warps, PREFETCH>;
-  constexpr int smem = kMma8Warps * kMma8WarpSmem;
+  auto kernel = stiffness_mma8_kernel<TS, P, IDENTITY, kMma8Warps, PREFETCH>;
+  constexpr int smem = kMma8Warps * Mma8Ring<TS>::WARP_SMEM;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -31,8 +31,8 @@ static int launch_mma8(const StiffnessArgs& a)
     blocks_per_sm[dev] = nb > 0 ? nb : 1;
   }
   Mma8Tables tab{};
-  const double* phi = static_cast<const double*>(a.phi0_host);   // [8][ND]
-  const double* dphi = static_cast<const double*>(a.dphi1_host); // [8][8]
+  const TS* phi = static_cast<const TS*>(a.phi0_host);   // [8][ND]
+  const TS* dphi = static_cast<const TS*>(a.dphi1_host); // [8][8]
   for (int q = 0; q < 8; ++q)
     for (int i = 0; i < 8; ++i)
     {
@@ -43,8 +43,8 @@ static int launch_mma8(const StiffnessArgs& a)
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
   const int grid = static_cast<int>(want < max_grid ? want : max_grid);
   kernel<<<grid, kMma8Warps * 32, smem, a.stream>>>(
-      static_cast<const double*>(a.u), static_cast<double*>(a.y), static_cast<const double*>(a.G),
-      static_cast<const double*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+      static_cast<const TS*>(a.u), static_cast<TS*>(a.y), static_cast<const TS*>(a.G),
+      static_cast<const TS*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
   BD_CUDA_CHECK(cudaGetLastError());
   return BD_SUCCESS;
 }
@@ -55,22 +55,22 @@ static int env_int(const char* name, int dflt)
   return e ? std::atoi(e) : dflt;
 }
 
-template <int P, bool IDENTITY>
+template <typename TS, int P, bool IDENTITY>
 static int launch_mma8_tuned(const StiffnessArgs& a)
 {
   // tuning knobs for experiments: BD_MMA8_WARPS (2|4 warps per CTA), BD_MMA8_PREFETCH (0|1)
   static const int warps = env_int("BD_MMA8_WARPS", 4), prefetch = env_int("BD_MMA8_PREFETCH", 1);
   if (warps == 4)
-    return prefetch ? launch_mma8<P, IDENTITY, 4, true>(a) : launch_mma8<P, IDENTITY, 4, false>(a);
-  return prefetch ? launch_mma8<P, IDENTITY, 2, true>(a) : launch_mma8<P, IDENTITY, 2, false>(a);
+    return prefetch ? launch_mma8<TS, P, IDENTITY, 4, true>(a) : launch_mma8<TS, P, IDENTITY, 4, false>(a);
+  return prefetch ? launch_mma8<TS, P, IDENTITY, 2, true>(a) : launch_mma8<TS, P, IDENTITY, 2, false>(a);
 }
 
-int launch_stiffness_mma8(int degree, bool identity, const StiffnessArgs& a)
+int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const StiffnessArgs& a)
 {
   if (degree == 6 && !identity)
-    return launch_mma8_tuned<6, false>(a);
+    return scalar_bits == 64 ? launch_mma8_tuned<double, 6, false>(a) : launch_mma8_tuned<float, 6, false>(a);
   if (degree == 7 && identity)
-    return launch_mma8_tuned<7, true>(a);
+    return scalar_bits == 64 ? launch_mma8_tuned<double, 7, true>(a) : launch_mma8_tuned<float, 7, true>(a);
   return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers degree 6 / qmode 1 and degree 7 / qmode 0 only");
 }
 } // namespace bd

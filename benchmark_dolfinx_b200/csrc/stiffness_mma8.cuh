@@ -34,9 +34,17 @@ struct Mma8Tables
   double dphi[64]; // dphi1[q][r], 8 x 8
 };
 
-constexpr int kMma8Stages = 4;
-constexpr int kMma8SlotBytes = 6 * 2 * 32 * 8; // one y-tile of G: 6 components x 2 registers x 32 lanes
-constexpr int kMma8WarpSmem = kMma8Stages * kMma8SlotBytes + 64;
+// Storage type TS may be float: the vectors and G are then read/written as float and converted, the
+// arithmetic stays fp64 on the tensor cores (there is no fp32 MMA short of TF32, and this fp64 path is
+// faster than fp32 SIMT contractions for nq = 8 while being more accurate than fp32 arithmetic).
+constexpr int kMma8SlotScalars = 6 * 2 * 32; // one y-tile of G: 6 components x 2 registers x 32 lanes
+template <typename TS>
+struct Mma8Ring
+{
+  static constexpr int STAGES = sizeof(TS) == 8 ? 4 : 8; // 12 KB per warp either way
+  static constexpr int SLOT_BYTES = kMma8SlotScalars * int(sizeof(TS));
+  static constexpr int WARP_SMEM = STAGES * SLOT_BYTES + 128;
+};
 constexpr std::int64_t kMma8CellG = 8 * 6 * 2 * 32; // doubles of G per cell
 
 // Position of (cell pos, comp, q0, q1, q2) in the accumulator-order G layout.
@@ -96,25 +104,27 @@ __device__ __forceinline__ void mma8_tile(const double (&M)[64], const double (&
   }
 }
 
-template <int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
+template <typename TS, int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 __global__ void __launch_bounds__(kMma8Warps * 32)
-    stiffness_mma8_kernel(const double* __restrict__ u, double* __restrict__ y, const double* __restrict__ Gf,
-                          const double* __restrict__ cell_constants,
+    stiffness_mma8_kernel(const TS* __restrict__ u, TS* __restrict__ y, const TS* __restrict__ Gf,
+                          const TS* __restrict__ cell_constants,
                           const std::int32_t* __restrict__ mdofmap, const std::int32_t* __restrict__ cells,
                           int ncells, const __grid_constant__ Mma8Tables tab)
 {
   constexpr int ND = P + 1;
   static_assert((ND == 7 && !IDENTITY) || (ND == 8 && IDENTITY), "nq = 8 only");
   constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
-  constexpr int NSTAGE = kMma8Stages;
-  constexpr int SLOT = kMma8SlotBytes / 8;
+  constexpr int NSTAGE = Mma8Ring<TS>::STAGES;
+  constexpr int SLOT = kMma8SlotScalars;
+  constexpr int kMma8SlotBytes = Mma8Ring<TS>::SLOT_BYTES;
+  constexpr int kMma8WarpSmem = Mma8Ring<TS>::WARP_SMEM;
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   unsigned char* wbase = smem_raw + warp * kMma8WarpSmem;
-  double* ring = reinterpret_cast<double*>(wbase);
+  TS* ring = reinterpret_cast<TS*>(wbase);
   std::uint64_t* bars = reinterpret_cast<std::uint64_t*>(wbase + NSTAGE * kMma8SlotBytes);
 
   // constant operand fragments
@@ -151,7 +161,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
   auto issue = [&](int s) {
     const int k = s >> 3, tile = s & 7;
     const std::int64_t pos = first + static_cast<std::int64_t>(k) * warps_total;
-    const double* src = Gf + pos * kMma8CellG + static_cast<std::int64_t>(tile) * SLOT;
+    const TS* src = Gf + pos * kMma8CellG + static_cast<std::int64_t>(tile) * SLOT;
     const int st = s % NSTAGE;
     mbar_expect_tx(bars + st, kMma8SlotBytes);
     bulk_copy_g2s(ring + st * SLOT, src, kMma8SlotBytes, bars + st);
@@ -178,7 +188,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
   // cell index and kappa are loaded one / two cells ahead (first-use stalls otherwise)
   std::int32_t cell_cur = my_cells > 0 ? cells[first] : 0;
   std::int32_t cell_next = my_cells > 1 ? cells[first + warps_total] : 0;
-  double kappa = my_cells > 0 ? cell_constants[first] : 0.0;
+  double kappa = my_cells > 0 ? static_cast<double>(cell_constants[first]) : 0.0;
   if (PREFETCH && my_cells > 0)
     load_dofs(cell_cur, ndof);
 
@@ -187,7 +197,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
   {
     const int pos = first + k * warps_total;
     const std::int32_t cell_next2 = k + 2 < my_cells ? cells[pos + 2 * warps_total] : 0;
-    const double kappa_next = k + 1 < my_cells ? cell_constants[pos + warps_total] : 0.0;
+    const double kappa_next = k + 1 < my_cells ? static_cast<double>(cell_constants[pos + warps_total]) : 0.0;
 
     // ---- gather: T[x = g][y][z = 2t + s], zero outside the ND^3 dofs and on constrained dofs
     double T[8][2];
@@ -210,7 +220,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       {
         const int z = 2 * t + s;
         const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
-        T[yy][s] = valid ? u[dof[yy][s] & 0x7fffffff] : 0.0;
+        T[yy][s] = valid ? static_cast<double>(u[dof[yy][s] & 0x7fffffff]) : 0.0;
       }
     // the next cell's indices travel while this cell is computed
     if (PREFETCH && k + 1 < my_cells)
@@ -224,7 +234,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
         const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
         if (valid && dof[yy][s] < 0)
         {
-          y[dof[yy][s] & 0x7fffffff] = T[yy][s]; // b[dof] = u[dof] on constrained dofs (reference :163-166)
+          y[dof[yy][s] & 0x7fffffff] = static_cast<TS>(T[yy][s]); // b[dof] = u[dof] on constrained dofs (reference :163-166)
           T[yy][s] = 0;
         }
       }
@@ -261,7 +271,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       mma8_col(gz0, gz1, T[yy][0], T[yy][1], d_col);
       const int st = slot % NSTAGE;
       mbar_wait(bars + st, (slot / NSTAGE) & 1);
-      const double* gs = ring + st * SLOT + lane; // [comp][s][lane]
+      const TS* gs = ring + st * SLOT + lane; // [comp][s][lane]
       double fx[2], fz[2];
 #pragma unroll
       for (int s = 0; s < 2; ++s)
@@ -306,7 +316,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
 #pragma unroll
       for (int s = 0; s < 2; ++s)
         if (dof[yy][s] >= 0)
-          atomicAdd(y + dof[yy][s], R[yy][s]);
+          atomicAdd(y + dof[yy][s], static_cast<TS>(R[yy][s]));
     cell_cur = cell_next;
     cell_next = cell_next2;
     kappa = kappa_next;
@@ -314,7 +324,20 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
 }
 
 // Geometry tensor in accumulator order from the reference layout (tests) and back.
+template <typename T>
 __global__ void __launch_bounds__(256)
-    mma8_g_to_reference_kernel(const double* __restrict__ Gf, double* __restrict__ G, std::int64_t ncells);
+    mma8_g_to_reference_kernel(const T* __restrict__ Gf, T* __restrict__ G, std::int64_t ncells)
+{
+  const std::int64_t total = ncells * 6 * 512;
+  const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
+  for (std::int64_t idx = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+       idx += stride)
+  {
+    const std::int64_t pos = idx / 3072;
+    const int rem = static_cast<int>(idx - pos * 3072);
+    const int comp = rem / 512, q = rem % 512;
+    G[idx] = Gf[mma8_g_index(pos, comp, q / 64, (q / 8) % 8, q % 8)];
+  }
+}
 
 } // namespace bd
