@@ -71,13 +71,12 @@ __global__ void __launch_bounds__(256)
     if constexpr (LAYOUT == 2)
     {
       const int q0 = q / (nq * nq), q1 = (q / nq) % nq, q2 = q % nq;
-      T* g = G + mma8_g_index(c, 0, q0, q1, q2);
-      g[0] = g0;
-      g[64] = g1;
-      g[128] = g2;
-      g[192] = g3;
-      g[256] = g4;
-      g[320] = g5;
+      G[mma8_g_index(nq, c, 0, q0, q1, q2)] = g0;
+      G[mma8_g_index(nq, c, 1, q0, q1, q2)] = g1;
+      G[mma8_g_index(nq, c, 2, q0, q1, q2)] = g2;
+      G[mma8_g_index(nq, c, 3, q0, q1, q2)] = g3;
+      G[mma8_g_index(nq, c, 4, q0, q1, q2)] = g4;
+      G[mma8_g_index(nq, c, 5, q0, q1, q2)] = g5;
     }
     else if constexpr (LAYOUT == 1)
     {
@@ -149,10 +148,10 @@ int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std:
   if (layout == 2)
   {
     if (scalar_bits == 64)
-      mma8_g_to_reference_kernel<double><<<grid, 256, 0, stream>>>(static_cast<const double*>(Gs),
+      mma8_g_to_reference_kernel<double><<<grid, 256, 0, stream>>>(nq, static_cast<const double*>(Gs),
                                                                   static_cast<double*>(G), ncells);
     else
-      mma8_g_to_reference_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(Gs),
+      mma8_g_to_reference_kernel<float><<<grid, 256, 0, stream>>>(nq, static_cast<const float*>(Gs),
                                                                  static_cast<float*>(G), ncells);
     BD_CUDA_CHECK(cudaGetLastError());
     return BD_SUCCESS;

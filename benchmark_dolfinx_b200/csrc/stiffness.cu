@@ -1,5 +1,6 @@
 // Dispatch + C entry point for the stiffness kernel.
 #include "stiffness_launch.cuh"
+#include "stiffness_mma8.cuh"
 
 #include <cstdlib>
 #include <cstring>
@@ -47,7 +48,7 @@ int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::i
 
 int preferred_g_layout(int scalar_bits, int nq)
 {
-  if (nq == 8 && stiffness_variant() != 1)
+  if ((nq == 8 || nq == 7) && stiffness_variant() != 1)
     return 2;
   return 1;
 }
@@ -55,7 +56,7 @@ int preferred_g_layout(int scalar_bits, int nq)
 std::int64_t g_layout_size(int layout, int nq, std::int64_t ncells)
 {
   if (layout == 2)
-    return ncells * 3072;
+    return ncells * mma8_cell_scalars(nq);
   if (layout == 1)
     return slab_g_size(nq, ncells);
   return ncells * 6 * nq * nq * nq;
@@ -65,8 +66,8 @@ int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const
 {
   if (a.g_layout == 2)
   {
-    if (nq != 8)
-      return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA layout needs nq = 8");
+    if (nq != 8 && nq != 7)
+      return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA layout needs nq = 7 or 8");
     return launch_stiffness_mma8(scalar_bits, degree, identity, a);
   }
   if (scalar_bits != 32 && scalar_bits != 64)

@@ -6,7 +6,7 @@
 
 namespace bd
 {
-template <typename TS, int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
+template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 static int launch_mma8(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
@@ -16,8 +16,8 @@ static int launch_mma8(const StiffnessArgs& a)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap)
     return fail(BD_ERR_INVALID_ARGUMENT, "the DMMA kernel needs the masked dofmap");
-  auto kernel = stiffness_mma8_kernel<TS, P, IDENTITY, kMma8Warps, PREFETCH>;
-  constexpr int smem = kMma8Warps * Mma8Ring<TS>::WARP_SMEM;
+  auto kernel = stiffness_mma8_kernel<TS, P, NQ, IDENTITY, kMma8Warps, PREFETCH>;
+  constexpr int smem = kMma8Warps * Mma8Ring<TS, NQ>::WARP_SMEM;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -31,13 +31,13 @@ static int launch_mma8(const StiffnessArgs& a)
     blocks_per_sm[dev] = nb > 0 ? nb : 1;
   }
   Mma8Tables tab{};
-  const TS* phi = static_cast<const TS*>(a.phi0_host);   // [8][ND]
-  const TS* dphi = static_cast<const TS*>(a.dphi1_host); // [8][8]
+  const TS* phi = static_cast<const TS*>(a.phi0_host);   // [NQ][ND]
+  const TS* dphi = static_cast<const TS*>(a.dphi1_host); // [NQ][NQ]
   for (int q = 0; q < 8; ++q)
     for (int i = 0; i < 8; ++i)
     {
-      tab.phi[q * 8 + i] = i < ND ? phi[q * ND + i] : 0.0;
-      tab.dphi[q * 8 + i] = dphi[q * 8 + i];
+      tab.phi[q * 8 + i] = (q < NQ && i < ND) ? phi[q * ND + i] : 0.0;
+      tab.dphi[q * 8 + i] = (q < NQ && i < NQ) ? dphi[q * NQ + i] : 0.0;
     }
   const std::int64_t want = (a.ncells + kMma8Warps - 1) / kMma8Warps;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
@@ -55,22 +55,26 @@ static int env_int(const char* name, int dflt)
   return e ? std::atoi(e) : dflt;
 }
 
-template <typename TS, int P, bool IDENTITY>
+template <typename TS, int P, int NQ, bool IDENTITY>
 static int launch_mma8_tuned(const StiffnessArgs& a)
 {
   // tuning knobs for experiments: BD_MMA8_WARPS (2|4 warps per CTA), BD_MMA8_PREFETCH (0|1)
   static const int warps = env_int("BD_MMA8_WARPS", 4), prefetch = env_int("BD_MMA8_PREFETCH", 1);
   if (warps == 4)
-    return prefetch ? launch_mma8<TS, P, IDENTITY, 4, true>(a) : launch_mma8<TS, P, IDENTITY, 4, false>(a);
-  return prefetch ? launch_mma8<TS, P, IDENTITY, 2, true>(a) : launch_mma8<TS, P, IDENTITY, 2, false>(a);
+    return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 4, true>(a) : launch_mma8<TS, P, NQ, IDENTITY, 4, false>(a);
+  return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 2, true>(a) : launch_mma8<TS, P, NQ, IDENTITY, 2, false>(a);
 }
 
 int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const StiffnessArgs& a)
 {
-  if (degree == 6 && !identity)
-    return scalar_bits == 64 ? launch_mma8_tuned<double, 6, false>(a) : launch_mma8_tuned<float, 6, false>(a);
-  if (degree == 7 && identity)
-    return scalar_bits == 64 ? launch_mma8_tuned<double, 7, true>(a) : launch_mma8_tuned<float, 7, true>(a);
-  return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers degree 6 / qmode 1 and degree 7 / qmode 0 only");
+#define BD_MMA8_CASE(P, NQ, ID)                                                                    \
+  if (degree == P && identity == ID)                                                               \
+    return scalar_bits == 64 ? launch_mma8_tuned<double, P, NQ, ID>(a) : launch_mma8_tuned<float, P, NQ, ID>(a);
+  BD_MMA8_CASE(6, 8, false)
+  BD_MMA8_CASE(7, 8, true)
+  BD_MMA8_CASE(5, 7, false)
+  BD_MMA8_CASE(6, 7, true)
+#undef BD_MMA8_CASE
+  return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers nq = 7 and nq = 8 only");
 }
 } // namespace bd

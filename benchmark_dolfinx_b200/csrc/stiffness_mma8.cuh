@@ -1,5 +1,6 @@
-// fp64 tensor-core (DMMA) stiffness action for 8 quadrature points per direction
-// (degree 6 with qmode 1, degree 7 with qmode 0), sm_100a.
+// fp64 tensor-core (DMMA) stiffness action for 8 quadrature points per direction (degree 6 with
+// qmode 1, degree 7 with qmode 0) and, with one padded lane group, for 7 (degree 5 with qmode 1,
+// degree 6 with qmode 0), sm_100a.
 //
 // Why: for nq = 8 the slab kernel is limited by per-thread state (49-64 values per dof plane ->
 // spills, 4 warps per SM) and reaches ~20 % of the HBM roofline (profiles/r1_v4_*), while the
@@ -37,21 +38,29 @@ struct Mma8Tables
 // Storage type TS may be float: the vectors and G are then read/written as float and converted, the
 // arithmetic stays fp64 on the tensor cores (there is no fp32 MMA short of TF32, and this fp64 path is
 // faster than fp32 SIMT contractions for nq = 8 while being more accurate than fp32 arithmetic).
-constexpr int kMma8SlotScalars = 6 * 2 * 32; // one y-tile of G: 6 components x 2 registers x 32 lanes
-template <typename TS>
+// One ring slot = one y-tile of G.  nq = 8: 6 components x 2 registers x 32 lanes in accumulator
+// order.  nq = 7 (one padded lane group): only the 7 x 7 real points of the tile are stored,
+// [comp][q0][q2], rounded up to a multiple of 4 scalars so every slot is a 16-byte multiple.
+__host__ __device__ constexpr int mma8_slot_scalars(int nq)
+{
+  return nq == 8 ? 6 * 2 * 32 : (6 * nq * nq + 3) / 4 * 4;
+}
+template <typename TS, int NQ>
 struct Mma8Ring
 {
-  static constexpr int STAGES = sizeof(TS) == 8 ? 4 : 8; // 12 KB per warp either way
-  static constexpr int SLOT_BYTES = kMma8SlotScalars * int(sizeof(TS));
+  static constexpr int STAGES = sizeof(TS) == 8 ? 4 : 8; // ~12 KB per warp either way
+  static constexpr int SLOT = mma8_slot_scalars(NQ);
+  static constexpr int SLOT_BYTES = SLOT * int(sizeof(TS));
   static constexpr int WARP_SMEM = STAGES * SLOT_BYTES + 128;
 };
-constexpr std::int64_t kMma8CellG = 8 * 6 * 2 * 32; // doubles of G per cell
-
-// Position of (cell pos, comp, q0, q1, q2) in the accumulator-order G layout.
-__host__ __device__ inline std::int64_t mma8_g_index(std::int64_t pos, int comp, int q0, int q1, int q2)
+// Scalars of G per cell and position of (cell pos, comp, q0, q1, q2) in the DMMA G layout.
+__host__ __device__ constexpr std::int64_t mma8_cell_scalars(int nq) { return std::int64_t(nq) * mma8_slot_scalars(nq); }
+__host__ __device__ inline std::int64_t mma8_g_index(int nq, std::int64_t pos, int comp, int q0, int q1, int q2)
 {
-  const int lane = 4 * q0 + (q2 >> 1), s = q2 & 1;
-  return pos * kMma8CellG + ((static_cast<std::int64_t>(q1) * 6 + comp) * 2 + s) * 32 + lane;
+  const std::int64_t base = pos * mma8_cell_scalars(nq) + static_cast<std::int64_t>(q1) * mma8_slot_scalars(nq);
+  if (nq == 8)
+    return base + (comp * 2 + (q2 & 1)) * 32 + 4 * q0 + (q2 >> 1);
+  return base + comp * nq * nq + q0 * nq + q2;
 }
 
 __device__ __forceinline__ void dmma(double& d0, double& d1, double a, double b)
@@ -104,7 +113,7 @@ __device__ __forceinline__ void mma8_tile(const double (&M)[64], const double (&
   }
 }
 
-template <typename TS, int P, bool IDENTITY, int kMma8Warps, bool PREFETCH>
+template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 __global__ void __launch_bounds__(kMma8Warps * 32)
     stiffness_mma8_kernel(const TS* __restrict__ u, TS* __restrict__ y, const TS* __restrict__ Gf,
                           const TS* __restrict__ cell_constants,
@@ -112,12 +121,14 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
                           int ncells, const __grid_constant__ Mma8Tables tab)
 {
   constexpr int ND = P + 1;
-  static_assert((ND == 7 && !IDENTITY) || (ND == 8 && IDENTITY), "nq = 8 only");
+  static_assert((NQ == 7 || NQ == 8) && ND <= NQ && IDENTITY == (ND == NQ), "nq = 7 or 8");
   constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
-  constexpr int NSTAGE = Mma8Ring<TS>::STAGES;
-  constexpr int SLOT = kMma8SlotScalars;
-  constexpr int kMma8SlotBytes = Mma8Ring<TS>::SLOT_BYTES;
-  constexpr int kMma8WarpSmem = Mma8Ring<TS>::WARP_SMEM;
+  using Ring = Mma8Ring<TS, NQ>;
+  constexpr int NSTAGE = Ring::STAGES;
+  constexpr int SLOT = Ring::SLOT;
+  constexpr int kMma8SlotBytes = Ring::SLOT_BYTES;
+  constexpr int kMma8WarpSmem = Ring::WARP_SMEM;
+  constexpr std::int64_t kMma8CellG = mma8_cell_scalars(NQ);
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;
@@ -148,7 +159,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
   const int warps_total = gridDim.x * kMma8Warps;
   const int first = blockIdx.x * kMma8Warps + warp;
   const int my_cells = first < ncells ? (ncells - first + warps_total - 1) / warps_total : 0;
-  const int total_slots = my_cells * 8;
+  const int total_slots = my_cells * NQ;
 
   if (lane == 0)
   {
@@ -159,7 +170,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
   }
   __syncwarp();
   auto issue = [&](int s) {
-    const int k = s >> 3, tile = s & 7;
+    const int k = s / NQ, tile = s - k * NQ;
     const std::int64_t pos = first + static_cast<std::int64_t>(k) * warps_total;
     const TS* src = Gf + pos * kMma8CellG + static_cast<std::int64_t>(tile) * SLOT;
     const int st = s % NSTAGE;
@@ -262,8 +273,15 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
     mma8_tile<false, false>(tab.dphi, T, F);
     double R[8][2];
 #pragma unroll
-    for (int yy = 0; yy < 8; ++yy, ++slot)
+    for (int yy = 0; yy < 8; ++yy)
     {
+      if (yy >= NQ)
+      {
+        // padded tile (nq = 7): no quadrature points, nothing to add
+        F[yy][0] = F[yy][1] = 0;
+        R[yy][0] = R[yy][1] = 0;
+        continue;
+      }
       if (lane == 0 && slot + NSTAGE - 1 < total_slots)
         issue(slot + NSTAGE - 1);
       double gx0, gx1, gz0, gz1;
@@ -271,19 +289,36 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       mma8_col(gz0, gz1, T[yy][0], T[yy][1], d_col);
       const int st = slot % NSTAGE;
       mbar_wait(bars + st, (slot / NSTAGE) & 1);
-      const TS* gs = ring + st * SLOT + lane; // [comp][s][lane]
       double fx[2], fz[2];
 #pragma unroll
       for (int s = 0; s < 2; ++s)
       {
-        const double G0 = gs[(0 * 2 + s) * 32], G1 = gs[(1 * 2 + s) * 32], G2 = gs[(2 * 2 + s) * 32];
-        const double G3 = gs[(3 * 2 + s) * 32], G4 = gs[(4 * 2 + s) * 32], G5 = gs[(5 * 2 + s) * 32];
+        double G0, G1, G2, G3, G4, G5;
+        if constexpr (NQ == 8)
+        {
+          const TS* gs = ring + st * SLOT + lane; // [comp][s][lane]
+          G0 = gs[(0 * 2 + s) * 32], G1 = gs[(1 * 2 + s) * 32], G2 = gs[(2 * 2 + s) * 32];
+          G3 = gs[(3 * 2 + s) * 32], G4 = gs[(4 * 2 + s) * 32], G5 = gs[(5 * 2 + s) * 32];
+        }
+        else
+        {
+          // [comp][q0 = g][q2 = 2t + s]; lanes of the padded group read nothing and get G = 0
+          const bool real = g < NQ && 2 * t + s < NQ;
+          const TS* gs = ring + st * SLOT + (real ? g * NQ + 2 * t + s : 0);
+          G0 = real ? static_cast<double>(gs[0 * NQ * NQ]) : 0.0;
+          G1 = real ? static_cast<double>(gs[1 * NQ * NQ]) : 0.0;
+          G2 = real ? static_cast<double>(gs[2 * NQ * NQ]) : 0.0;
+          G3 = real ? static_cast<double>(gs[3 * NQ * NQ]) : 0.0;
+          G4 = real ? static_cast<double>(gs[4 * NQ * NQ]) : 0.0;
+          G5 = real ? static_cast<double>(gs[5 * NQ * NQ]) : 0.0;
+        }
         const double gx = s ? gx1 : gx0, gy = F[yy][s], gz = s ? gz1 : gz0;
         fx[s] = kappa * (G0 * gx + G1 * gy + G2 * gz);
         F[yy][s] = kappa * (G1 * gx + G3 * gy + G4 * gz);
         fz[s] = kappa * (G2 * gx + G4 * gy + G5 * gz);
       }
       __syncwarp(); // every lane is done with slot `st` before it is refilled
+      ++slot;
       double rx0, rx1, rz0, rz1;
       mma8_row(rx0, rx1, fx[0], fx[1], dT_row, src0, src1, odd);
       mma8_col(rz0, rz1, fz[0], fz[1], dT_col);
@@ -326,17 +361,18 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
 // Geometry tensor in accumulator order from the reference layout (tests) and back.
 template <typename T>
 __global__ void __launch_bounds__(256)
-    mma8_g_to_reference_kernel(const T* __restrict__ Gf, T* __restrict__ G, std::int64_t ncells)
+    mma8_g_to_reference_kernel(int nq, const T* __restrict__ Gf, T* __restrict__ G, std::int64_t ncells)
 {
-  const std::int64_t total = ncells * 6 * 512;
+  const int nq3 = nq * nq * nq;
+  const std::int64_t total = ncells * 6 * nq3;
   const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
   for (std::int64_t idx = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
        idx += stride)
   {
-    const std::int64_t pos = idx / 3072;
-    const int rem = static_cast<int>(idx - pos * 3072);
-    const int comp = rem / 512, q = rem % 512;
-    G[idx] = Gf[mma8_g_index(pos, comp, q / 64, (q / 8) % 8, q % 8)];
+    const std::int64_t pos = idx / (6 * nq3);
+    const int rem = static_cast<int>(idx - pos * (6 * nq3));
+    const int comp = rem / nq3, q = rem % nq3;
+    G[idx] = Gf[mma8_g_index(nq, pos, comp, q / (nq * nq), (q / nq) % nq, q % nq)];
   }
 }
 
