@@ -46,6 +46,15 @@ int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::i
   return BD_SUCCESS;
 }
 
+int slab_tune_variant()
+{
+  static const int v = [] {
+    const char* e = std::getenv("BD_SLAB_TUNE");
+    return e ? std::atoi(e) : 0;
+  }();
+  return v;
+}
+
 int preferred_g_layout(int scalar_bits, int nq)
 {
   if ((nq == 8 || nq == 7) && stiffness_variant() != 1)

@@ -95,20 +95,18 @@ void fill_slab_tables(SlabTables<T, ND, NQ>& tab, const void* phi0_host, const v
 template <int NQ>
 struct SlabTmaTuning
 {
-  static constexpr int NSTAGE = NQ <= 5 ? 3 : 4;
+  static constexpr int NSTAGE = NQ <= 5 ? 2 : 4;
   static constexpr int Q0C = NQ <= 5 ? NQ : (NQ == 6 ? 3 : (NQ == 8 ? 2 : (NQ == 9 ? 3 : NQ)));
-  static constexpr int WARPS = NQ <= 5 ? 2 : 1;
+  static constexpr int WARPS = 1;
   static constexpr bool PREFETCH = NQ <= 5;
 };
 
-// Slab kernel with the G stream on asynchronous bulk copies (stiffness_slab.cuh).
-template <typename T, int P, int NQ, bool IDENTITY>
-int launch_stiffness_slab_tma(const StiffnessArgs& a)
+// Slab kernel with the G stream on asynchronous bulk copies (stiffness_slab.cuh), explicit tuning.
+template <typename T, int P, int NQ, bool IDENTITY, int NSTAGE, int Q0C_, int WARPS_, bool PREFETCH_>
+int launch_stiffness_slab_tma_cfg(const StiffnessArgs& a)
 {
   using C = SlabConfig<T, P, NQ>;
-  using TU = SlabTmaTuning<NQ>;
-  constexpr int NSTAGE = (NQ == 7) ? 2 : TU::NSTAGE;
-  using TC = SlabTmaConfig<T, P, NQ, NSTAGE, TU::Q0C, TU::WARPS>;
+  using TC = SlabTmaConfig<T, P, NQ, NSTAGE, Q0C_, WARPS_>;
   constexpr int ND = P + 1;
   if constexpr (!TC::SUPPORTED)
     return fail(BD_ERR_UNSUPPORTED, "asynchronous-copy slab kernel unsupported for this configuration");
@@ -116,7 +114,7 @@ int launch_stiffness_slab_tma(const StiffnessArgs& a)
   {
     if (!a.mdofmap)
       return fail(BD_ERR_INVALID_ARGUMENT, "the asynchronous-copy kernel needs the masked dofmap");
-    auto kernel = stiffness_slab_tma_kernel<T, P, NQ, IDENTITY, NSTAGE, TU::Q0C, TU::WARPS, TU::PREFETCH>;
+    auto kernel = stiffness_slab_tma_kernel<T, P, NQ, IDENTITY, NSTAGE, Q0C_, WARPS_, PREFETCH_>;
     static thread_local int blocks_per_sm[64] = {0};
     int dev = 0;
     BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -141,6 +139,23 @@ int launch_stiffness_slab_tma(const StiffnessArgs& a)
     BD_CUDA_CHECK(cudaGetLastError());
     return BD_SUCCESS;
   }
+}
+
+int slab_tune_variant(); // env BD_SLAB_TUNE (experiments), 0 = default
+
+template <typename T, int P, int NQ, bool IDENTITY>
+int launch_stiffness_slab_tma(const StiffnessArgs& a)
+{
+  using TU = SlabTmaTuning<NQ>;
+  constexpr int NSTAGE = (NQ == 7) ? 2 : TU::NSTAGE;
+  if constexpr (NQ <= 5)
+  {
+    // experiments: BD_SLAB_TUNE=1 -> ring of 3 slots, 2 warps per CTA (6 warps/SM at Q3 fp64);
+    // default   -> ring of 2 slots, 1 warp per CTA (7 warps/SM): measured 15.2 vs 16.1 ms at Q3/300M
+    if (slab_tune_variant() == 1)
+      return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, 3, NQ, 2, true>(a);
+  }
+  return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, NSTAGE, TU::Q0C, TU::WARPS, TU::PREFETCH>(a);
 }
 
 template <typename T, int P, int NQ>

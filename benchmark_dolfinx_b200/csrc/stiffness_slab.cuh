@@ -179,10 +179,13 @@ __device__ __forceinline__ void slab_forward_x(const SlabTables<T, ND, NQ>& tab,
 // Z phase of lane (c, q2) for one q1 and the q0 range [Q0B, Q0B + Q0N): x contractions, G, kappa,
 // transposed x contractions accumulated into bx, by, bz.  G values come from `g` (global or shared
 // memory), element (q0 - Q0B, comp) at g[((q0 - Q0B)*6 + comp)*ROW].
-template <typename T, int ND, int NQ, int ROW, bool IDENTITY, int Q0B, int Q0N, bool STREAM_LDG>
+// Q0B is an ordinary argument, but every call site sits in a fully unrolled loop, so after inlining
+// all table indices are compile-time constants.
+template <typename T, int ND, int NQ, int ROW, bool IDENTITY, int Q0N, bool STREAM_LDG>
 __device__ __forceinline__ void slab_z_points(const SlabTables<T, ND, NQ>& tab, const T (&ax)[ND],
                                               const T (&ay)[ND], const T (&az)[ND], T (&bx)[ND],
-                                              T (&by)[ND], T (&bz)[ND], const T* __restrict__ g, T kappa)
+                                              T (&by)[ND], T (&bz)[ND], const T* __restrict__ g, T kappa,
+                                              const int Q0B)
 {
 #pragma unroll
   for (int qq = 0; qq < Q0N; ++qq)
@@ -402,8 +405,8 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
           by[i] = 0;
           bz[i] = 0;
         }
-        slab_z_points<T, ND, NQ, C::ROW, IDENTITY, 0, NQ, true>(
-            tab, ax, ay, az, bx, by, bz, Gb + static_cast<std::int64_t>(q1) * (NQ * 6 * C::ROW), kappa);
+        slab_z_points<T, ND, NQ, C::ROW, IDENTITY, NQ, true>(
+            tab, ax, ay, az, bx, by, bz, Gb + static_cast<std::int64_t>(q1) * (NQ * 6 * C::ROW), kappa, 0);
 #pragma unroll
         for (int i = 0; i < ND; ++i)
         {
@@ -486,7 +489,7 @@ template <typename T, int P, int NQ, int NSTAGE, int Q0C, int WARPS_>
 struct SlabTmaConfig
 {
   using Base = SlabConfig<T, P, NQ>;
-  static_assert(NQ % Q0C == 0 && NQ / Q0C <= 4, "Q0C must divide NQ into at most 4 chunks");
+  static_assert(NQ % Q0C == 0, "Q0C must divide NQ");
   static constexpr int NCH = NQ / Q0C;                            // slots per q1 slice
   static constexpr int SLOT = Q0C * 6 * Base::ROW;                // scalars per slot
   static constexpr int SLOT_BYTES = SLOT * int(sizeof(T));
@@ -666,26 +669,7 @@ __global__ void __launch_bounds__(WARPS_ * 32)
         if (active)
         {
           const T* gs = ring + st * TC::SLOT + rbase + m;
-          // Q0B must be a compile-time constant: dispatch on the unrolled chunk index
-          if constexpr (NCH == 1)
-            slab_z_points<T, ND, NQ, ROW, IDENTITY, 0, Q0C, false>(tab, ax, ay, az, bx, by, bz, gs, kappa);
-          else
-          {
-            if (ch == 0)
-              slab_z_points<T, ND, NQ, ROW, IDENTITY, 0, Q0C, false>(tab, ax, ay, az, bx, by, bz, gs, kappa);
-            if constexpr (NCH > 1)
-              if (ch == 1)
-                slab_z_points<T, ND, NQ, ROW, IDENTITY, (NCH > 1 ? Q0C : 0), Q0C, false>(tab, ax, ay, az, bx,
-                                                                                      by, bz, gs, kappa);
-            if constexpr (NCH > 2)
-              if (ch == 2)
-                slab_z_points<T, ND, NQ, ROW, IDENTITY, (NCH > 2 ? 2 * Q0C : 0), Q0C, false>(
-                    tab, ax, ay, az, bx, by, bz, gs, kappa);
-            if constexpr (NCH > 3)
-              if (ch == 3)
-                slab_z_points<T, ND, NQ, ROW, IDENTITY, (NCH > 3 ? 3 * Q0C : 0), Q0C, false>(
-                    tab, ax, ay, az, bx, by, bz, gs, kappa);
-          }
+          slab_z_points<T, ND, NQ, ROW, IDENTITY, Q0C, false>(tab, ax, ay, az, bx, by, bz, gs, kappa, ch * Q0C);
         }
         __syncwarp(); // every lane is done with slot `st` before it is refilled
       }
