@@ -169,13 +169,14 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncwarp();
+  const std::uint64_t g_policy = l2_evict_first_policy();
   auto issue = [&](int s) {
     const int k = s / NQ, tile = s - k * NQ;
     const std::int64_t pos = first + static_cast<std::int64_t>(k) * warps_total;
     const TS* src = Gf + pos * kMma8CellG + static_cast<std::int64_t>(tile) * SLOT;
     const int st = s % NSTAGE;
     mbar_expect_tx(bars + st, kMma8SlotBytes);
-    bulk_copy_g2s(ring + st * SLOT, src, kMma8SlotBytes, bars + st);
+    bulk_copy_g2s_hint(ring + st * SLOT, src, kMma8SlotBytes, bars + st, g_policy);
   };
   if (lane == 0)
     for (int s = 0; s < NSTAGE - 1 && s < total_slots; ++s)

@@ -181,7 +181,7 @@ __device__ __forceinline__ void slab_forward_x(const SlabTables<T, ND, NQ>& tab,
 // memory), element (q0 - Q0B, comp) at g[((q0 - Q0B)*6 + comp)*ROW].
 // Q0B is an ordinary argument, but every call site sits in a fully unrolled loop, so after inlining
 // all table indices are compile-time constants.
-template <typename T, int ND, int NQ, int ROW, bool IDENTITY, int Q0N, bool STREAM_LDG>
+template <typename T, int ND, int NQ, int ROW, bool IDENTITY, int Q0N, bool STREAM_LDG, bool SCALE = true>
 __device__ __forceinline__ void slab_z_points(const SlabTables<T, ND, NQ>& tab, const T (&ax)[ND],
                                               const T (&ay)[ND], const T (&az)[ND], T (&bx)[ND],
                                               T (&by)[ND], T (&bz)[ND], const T* __restrict__ g, T kappa,
@@ -235,9 +235,17 @@ __device__ __forceinline__ void slab_z_points(const SlabTables<T, ND, NQ>& tab, 
       }
     }
     // reference src/laplacian_gpu.hpp:269-273
-    const T fx = kappa * (G0 * gx + G1 * gy + G2 * gz);
-    const T fy = kappa * (G1 * gx + G3 * gy + G4 * gz);
-    const T fz = kappa * (G2 * gx + G4 * gy + G5 * gz);
+    // SCALE = false: the caller has already multiplied the cell's input by kappa (the operator is
+    // linear in kappa), which saves three multiplies per quadrature point
+    T fx = G0 * gx + G1 * gy + G2 * gz;
+    T fy = G1 * gx + G3 * gy + G4 * gz;
+    T fz = G2 * gx + G4 * gy + G5 * gz;
+    if constexpr (SCALE)
+    {
+      fx *= kappa;
+      fy *= kappa;
+      fz *= kappa;
+    }
     if constexpr (IDENTITY)
     {
       by[q0] = fy;
@@ -469,6 +477,22 @@ __device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, std::u
                "l"(src), "r"(bytes), "r"(smem_addr(bar))
                : "memory");
 }
+// G is read exactly once per operator application: mark its lines evict-first in L2 so that the
+// 126 MB L2 keeps the re-used data (input/output vector planes shared by neighbouring cells, dofmap).
+__device__ __forceinline__ std::uint64_t l2_evict_first_policy()
+{
+  std::uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_copy_g2s_hint(void* dst, const void* src, std::uint32_t bytes,
+                                                   std::uint64_t* bar, std::uint64_t policy)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, "
+               "[%3], %4;" ::"r"(smem_addr(dst)),
+               "l"(src), "r"(bytes), "r"(smem_addr(bar)), "l"(policy)
+               : "memory");
+}
 __device__ __forceinline__ void mbar_wait(std::uint64_t* bar, std::uint32_t parity)
 {
   asm volatile("{\n"
@@ -543,6 +567,7 @@ __global__ void __launch_bounds__(WARPS_ * 32)
   }
   __syncwarp();
 
+  const std::uint64_t g_policy = l2_evict_first_policy();
   // slot s of this warp's stream = (batch first + k*warps_total, q1, chunk), s = (k*NQ + q1)*NCH + chunk;
   // within a batch the slots are consecutive in memory
   auto issue = [&](int s) {
@@ -551,7 +576,7 @@ __global__ void __launch_bounds__(WARPS_ * 32)
     const T* src = Gs + batch * C::G_BATCH + static_cast<std::int64_t>(r) * TC::SLOT;
     const int st = s % NSTAGE;
     mbar_expect_tx(bars + st, TC::SLOT_BYTES);
-    bulk_copy_g2s(ring + st * TC::SLOT, src, TC::SLOT_BYTES, bars + st);
+    bulk_copy_g2s_hint(ring + st * TC::SLOT, src, TC::SLOT_BYTES, bars + st, g_policy);
   };
   if (lane == 0)
   {
@@ -618,11 +643,14 @@ __global__ void __launch_bounds__(WARPS_ * 32)
     {
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
+      {
         if (dof[t] < 0)
         {
           y[dof[t] & 0x7fffffff] = ul[t];
           ul[t] = 0;
         }
+        ul[t] *= kappa; // kappa folded into the input: y = A(kappa) u = A(1) (kappa u)
+      }
       slab_forward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, ul, cube + m * RL + rbase);
     }
     __syncwarp();
@@ -636,12 +664,18 @@ __global__ void __launch_bounds__(WARPS_ * 32)
       load_dofs(nrow, ndof);
     }
 
+    // Middle phase.  When the padded row is at least 32 wide every lane runs it without a branch:
+    // the idle lanes of the warp (and teams past the end of the list) work on row entries nobody
+    // else uses -- lanes >= ROW sit in the padding columns -- and their results are never scattered.
+    constexpr bool ALL_LANES = RL >= 32;
+    const int zr = ALL_LANES ? lane : rbase + m;
+    const bool zactive = ALL_LANES || active;
 #pragma unroll 1
     for (int q1 = 0; q1 < NQ; ++q1)
     {
       T ax[ND], ay[ND], az[ND], bx[ND], by[ND], bz[ND];
-      T* src = cube + (q1 * ND) * RL + rbase + m;
-      if (active)
+      T* src = cube + (q1 * ND) * RL + zr;
+      if (zactive)
       {
 #pragma unroll
         for (int i = 0; i < ND; ++i)
@@ -666,14 +700,15 @@ __global__ void __launch_bounds__(WARPS_ * 32)
           issue(slot + NSTAGE - 1);
         const int st = slot % NSTAGE;
         mbar_wait(bars + st, (slot / NSTAGE) & 1);
-        if (active)
+        if (zactive)
         {
-          const T* gs = ring + st * TC::SLOT + rbase + m;
-          slab_z_points<T, ND, NQ, ROW, IDENTITY, Q0C, false>(tab, ax, ay, az, bx, by, bz, gs, kappa, ch * Q0C);
+          const T* gs = ring + st * TC::SLOT + zr;
+          slab_z_points<T, ND, NQ, ROW, IDENTITY, Q0C, false, false>(tab, ax, ay, az, bx, by, bz, gs, kappa,
+                                                                     ch * Q0C);
         }
         __syncwarp(); // every lane is done with slot `st` before it is refilled
       }
-      if (active)
+      if (zactive)
       {
 #pragma unroll
         for (int i = 0; i < ND; ++i)
