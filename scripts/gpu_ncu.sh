@@ -2,7 +2,8 @@ set -x
 mkdir -p gpurun_out
 make -C benchmark_dolfinx_b200 -j 16 2>&1 | tail -1
 DEG=${DEG:-3}; ND=${ND:-300000000}; TAG=${TAG:-v5}; FL=${FL:-64}
-ARGS="--degree $DEG --ndofs $ND --float $FL --steps 2 --warmup 3 --no-cpu --no-e2e"
+QM=${QM:-1}
+ARGS="--degree $DEG --ndofs $ND --float $FL --qmode $QM --steps 2 --warmup 3 --no-cpu --no-e2e"
 python bench.py $ARGS > gpurun_out/plain_q${DEG}_$TAG.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_q${DEG}_$TAG.csv python bench.py $ARGS > gpurun_out/ncu_list_q${DEG}_$TAG.log 2>&1
 echo "list rc=$?"
