@@ -95,7 +95,8 @@ void fill_slab_tables(SlabTables<T, ND, NQ>& tab, const void* phi0_host, const v
 template <int NQ>
 struct SlabTmaTuning
 {
-  static constexpr int NSTAGE = NQ <= 5 ? 2 : 4;
+  // measured (scripts/gpu_tune*.sh): nq <= 5: 2 slots of a whole q1 slice; nq = 6: 3 half-slice slots
+  static constexpr int NSTAGE = NQ <= 5 ? 2 : (NQ == 6 ? 3 : 4);
   static constexpr int Q0C = NQ <= 5 ? NQ : (NQ == 6 ? 3 : (NQ == 8 ? 2 : (NQ == 9 ? 3 : NQ)));
   static constexpr int WARPS = 1;
   static constexpr bool PREFETCH = NQ <= 5;
