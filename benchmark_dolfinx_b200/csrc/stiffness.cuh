@@ -99,18 +99,23 @@ __global__ void __launch_bounds__(block_threads(NQ))
 #pragma unroll
       for (int i = 0; i < ND; ++i)
         dof[i] = row[i * ND2];
+      // all loads first, then the (rare) stores to constrained dofs: a store in between would make
+      // the warp wait in order for each load
+      std::int8_t flag[ND];
 #pragma unroll
       for (int i = 0; i < ND; ++i)
       {
-        const T v = u[dof[i]];
-        if (bc[dof[i]])
-        {
-          y[dof[i]] = v; // b[dof] = u[dof] on constrained dofs
-          dof[i] = -1;
-        }
-        else
-          col[i] = v;
+        col[i] = u[dof[i]];
+        flag[i] = bc[dof[i]];
       }
+#pragma unroll
+      for (int i = 0; i < ND; ++i)
+        if (flag[i])
+        {
+          y[dof[i]] = col[i]; // b[dof] = u[dof] on constrained dofs
+          dof[i] = -1;
+          col[i] = 0;
+        }
     }
 
     if constexpr (!IDENTITY)

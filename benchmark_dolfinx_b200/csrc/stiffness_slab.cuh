@@ -376,19 +376,21 @@ __global__ void __launch_bounds__(SlabConfig<T, P, NQ>::THREADS)
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
         dof[t] = row[t];
+      std::int8_t flag[ND2];
+#pragma unroll
+      for (int t = 0; t < ND2; ++t) // loads first, stores after (see stiffness.cuh)
+      {
+        ul[t] = u[dof[t]];
+        flag[t] = bc[dof[t]];
+      }
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
-      {
-        const T v = u[dof[t]];
-        if (bc[dof[t]])
+        if (flag[t])
         {
-          y[dof[t]] = v; // b[dof] = u[dof] on constrained dofs
+          y[dof[t]] = ul[t]; // b[dof] = u[dof] on constrained dofs
           dof[t] = -1;
           ul[t] = 0;
         }
-        else
-          ul[t] = v;
-      }
       slab_forward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, ul, cube + m * RL + rbase);
     }
     __syncwarp();
