@@ -176,6 +176,105 @@ __device__ __forceinline__ void slab_forward_x(const SlabTables<T, ND, NQ>& tab,
   }
 }
 
+// Variants of the two X phases for large ND (nq = 9): the q2 loop is a real loop and the two table
+// rows it needs are fetched from the constant bank with a warp-uniform dynamic index.  Fully unrolled,
+// these phases are ~10k instructions each at ND = 8 and ncu shows the warps starving on instruction
+// fetch ("no instruction" = 3.4 of 7 stall cycles per issue) on top of register spills.
+template <typename T, int ND, int NQ, int RL, int CUBE>
+__device__ __forceinline__ void slab_forward_x_rolled(const SlabTables<T, ND, NQ>& tab, const T (&ul)[ND * ND],
+                                                      T* __restrict__ dst0)
+{
+#pragma unroll 1
+  for (int q2 = 0; q2 < NQ; ++q2)
+  {
+    T pr[ND], dr[ND];
+#pragma unroll
+    for (int k = 0; k < ND; ++k)
+    {
+      pr[k] = tab.phi[q2 * ND + k];
+      dr[k] = tab.dphi[q2 * ND + k];
+    }
+    T pz[ND], dz[ND];
+#pragma unroll
+    for (int j = 0; j < ND; ++j)
+    {
+      T s = 0, d = 0;
+#pragma unroll
+      for (int k = 0; k < ND; ++k)
+      {
+        s += pr[k] * ul[j * ND + k];
+        d += dr[k] * ul[j * ND + k];
+      }
+      pz[j] = s;
+      dz[j] = d;
+    }
+#pragma unroll
+    for (int q1 = 0; q1 < NQ; ++q1)
+    {
+      T ax = 0, ay = 0, az = 0;
+#pragma unroll
+      for (int j = 0; j < ND; ++j)
+      {
+        ax += tab.phi[q1 * ND + j] * pz[j];
+        ay += tab.dphi[q1 * ND + j] * pz[j];
+        az += tab.phi[q1 * ND + j] * dz[j];
+      }
+      T* dst = dst0 + q1 * (ND * RL) + q2;
+      dst[0] = ax;
+      dst[CUBE] = ay;
+      dst[2 * CUBE] = az;
+    }
+  }
+}
+
+template <typename T, int ND, int NQ, int RL, int CUBE>
+__device__ __forceinline__ void slab_backward_x_rolled(const SlabTables<T, ND, NQ>& tab,
+                                                       const T* __restrict__ src0, T (&out)[ND * ND])
+{
+#pragma unroll
+  for (int t = 0; t < ND * ND; ++t)
+    out[t] = 0;
+#pragma unroll 1
+  for (int q2 = 0; q2 < NQ; ++q2)
+  {
+    T e1[ND], e2[ND];
+#pragma unroll
+    for (int j = 0; j < ND; ++j)
+    {
+      e1[j] = 0;
+      e2[j] = 0;
+    }
+#pragma unroll
+    for (int q1 = 0; q1 < NQ; ++q1)
+    {
+      const T* src = src0 + q1 * (ND * RL) + q2;
+      const T bx = src[0], by = src[CUBE], bz = src[2 * CUBE];
+#pragma unroll
+      for (int j = 0; j < ND; ++j)
+      {
+        e1[j] += tab.phi[q1 * ND + j] * bx;
+        e1[j] += tab.dphi[q1 * ND + j] * by;
+        e2[j] += tab.phi[q1 * ND + j] * bz;
+      }
+    }
+    T pr[ND], dr[ND];
+#pragma unroll
+    for (int k = 0; k < ND; ++k)
+    {
+      pr[k] = tab.phi[q2 * ND + k];
+      dr[k] = tab.dphi[q2 * ND + k];
+    }
+#pragma unroll
+    for (int j = 0; j < ND; ++j)
+#pragma unroll
+      for (int k = 0; k < ND; ++k)
+      {
+        out[j * ND + k] += pr[k] * e1[j];
+        out[j * ND + k] += dr[k] * e2[j];
+      }
+  }
+}
+
 // Z phase of lane (c, q2) for one q1 and the q0 range [Q0B, Q0B + Q0N): x contractions, G, kappa,
 // transposed x contractions accumulated into bx, by, bz.  G values come from `g` (global or shared
 // memory), element (q0 - Q0B, comp) at g[((q0 - Q0B)*6 + comp)*ROW].
@@ -653,7 +752,10 @@ __global__ void __launch_bounds__(WARPS_ * 32)
         }
         ul[t] *= kappa; // kappa folded into the input: y = A(kappa) u = A(1) (kappa u)
       }
-      slab_forward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, ul, cube + m * RL + rbase);
+      if constexpr (NQ >= 9 && !IDENTITY)
+        slab_forward_x_rolled<T, ND, NQ, RL, CUBE>(tab, ul, cube + m * RL + rbase);
+      else
+        slab_forward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, ul, cube + m * RL + rbase);
     }
     __syncwarp();
 
@@ -731,7 +833,10 @@ __global__ void __launch_bounds__(WARPS_ * 32)
     if (xlane)
     {
       T out[ND2];
-      slab_backward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, cube + m * RL + rbase, out);
+      if constexpr (NQ >= 9 && !IDENTITY)
+        slab_backward_x_rolled<T, ND, NQ, RL, CUBE>(tab, cube + m * RL + rbase, out);
+      else
+        slab_backward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, cube + m * RL + rbase, out);
       if constexpr (PREFETCH)
       {
 #pragma unroll
