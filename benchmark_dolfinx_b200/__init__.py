@@ -178,7 +178,7 @@ class BoxMesh:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and lib is not None:          # module globals may be gone at interpreter exit
             lib.bd_boxmesh_destroy(h)
 
     # -- host copies (tests / small meshes)
@@ -243,7 +243,7 @@ class Comm:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and lib is not None:          # module globals may be gone at interpreter exit
             lib.bd_comm_destroy(h)
 
 
@@ -281,7 +281,7 @@ class Halo:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and lib is not None:          # module globals may be gone at interpreter exit
             lib.bd_halo_destroy(h)
 
 
@@ -339,7 +339,7 @@ class MatFreeLaplacianGPU:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and lib is not None:          # module globals may be gone at interpreter exit
             lib.bd_laplacian_destroy(h)
 
     def _check_vec(self, v):
@@ -415,7 +415,7 @@ class MatrixOperator:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and lib is not None:          # module globals may be gone at interpreter exit
             lib.bd_csr_destroy(h)
 
     _check_vec = MatFreeLaplacianGPU._check_vec
