@@ -217,6 +217,59 @@ def workload_config(args, world):
     }
 
 
+def reference_gpu_kernel_leg(bd, degree, qmode, dtype, ndofs, steps):
+    """GDoF/s of the reference's stiffness_operator_gpu<T,P,Q> (src/laplacian_gpu.hpp:91-426, launched as
+    src/laplacian.hpp:298-306: one CTA of (Q,Q,Q) threads per cell) and of our kernel on the same mesh."""
+    import torch
+    from oracle import native
+    ref = native.ref_gpu_lib()
+    if ref is None:
+        return {"value": None, "note": "oracle/_ref/libref_gpu.so not built"}
+    bits = 64 if dtype == np.float64 else 32
+    n = bd.compute_mesh_size(ndofs, degree)
+    mesh = bd.BoxMesh(n, degree, dtype=dtype)
+    op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype)
+    t = op.tables
+    import ctypes as C
+    from benchmark_dolfinx_b200 import _lib
+    gp, gn = C.c_void_p(), C.c_int64()
+    _lib.check(_lib.lib.bd_laplacian_geometry(op._h, C.byref(gp), C.byref(gn)))   # reference-layout copy of G
+    tdt = torch.float64 if bits == 64 else torch.float32
+    u = mesh.assemble_rhs(qmode)
+    y = torch.zeros_like(u)
+    consts = torch.full((mesh.ncells,), 2.0, dtype=tdt, device="cuda")
+    phi0, dphi1 = torch.from_numpy(t.phi0).cuda(), torch.from_numpy(t.dphi1).cuda()
+    i = mesh.info
+
+    def ref_apply():
+        y.zero_()
+        native.ref_gpu_stiffness(ref, degree, t.nq, t.is_identity, u.data_ptr(), y.data_ptr(), gp.value,
+                                 consts.data_ptr(), phi0.data_ptr(), dphi1.data_ptr(), i.cell_dofmap, i.lcells,
+                                 int(mesh.n_lcells), i.bc_marker, bits)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 1e3 / steps
+
+    t_ref = timed(ref_apply)
+    ynorm_ref = bd.norm(y)
+    t_ours = timed(lambda: op.apply(u, y))
+    ynorm = bd.norm(y)
+    return {"value": mesh.ndofs_global / (1e9 * t_ref), "unit": "GDoF/s", "ms_per_apply": 1e3 * t_ref,
+            "ours_same_mesh": mesh.ndofs_global / (1e9 * t_ours), "speedup": t_ref / t_ours,
+            "ndofs": mesh.ndofs_global, "y_norm_reference_kernel": ynorm_ref, "y_norm_ours": ynorm,
+            "kernel": f"benchdolfinx::stiffness_operator_gpu<{'double' if bits == 64 else 'float'},{degree},{t.nq}> "
+                      "(reference source, unmodified, -arch sm_100a; one CTA per cell)"}
+
+
 # ----------------------------------------------------------------------------- our arm
 def main():
     ap = argparse.ArgumentParser()
@@ -400,6 +453,17 @@ def main():
                if world == 1 else None}
         del uh, yh
 
+    # ---- the kernel to beat: the reference's own stiffness_operator_gpu (unmodified source recompiled for
+    #      sm_100a, oracle/_ref/libref_gpu.so) with its own launch shape, on a smaller mesh of the same
+    #      degree (its G layout needs a second copy of G), timed with CUDA events on the same GPU
+    ref_gpu = None
+    if world == 1 and rank == 0 and not args.no_cpu:
+        try:
+            ref_gpu = reference_gpu_kernel_leg(bd, degree, qmode, dtype, min(args.ndofs, 100_000_000),
+                                               max(3, min(args.steps, 10)))
+        except Exception as exc:
+            ref_gpu = {"value": None, "note": f"{type(exc).__name__}: {exc}"}
+
     # ---- CPU baseline: the reference's CPU kernels on this box's host cores (rank 0, N = 1)
     cpu = None
     if world == 1 and rank == 0 and not args.no_cpu:
@@ -420,6 +484,7 @@ def main():
             "config": dict(workload_config(args, world), ndofs_global_requested=args.ndofs_global or None, mesh_cells=n, ndofs_global=ndofs_global,
                            ncells_global=mesh.ncells_global, setup_seconds=t_setup),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cg": cg,
+            "reference_gpu_kernel": ref_gpu,
             "gpu_launches": gpu_launches, "clocks": clocks,
             "u_norm": unorm, "y_norm": ynorm,
         }

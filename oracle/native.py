@@ -22,6 +22,12 @@ def ref_lib(strict=False):
     return _load(os.path.join(_HERE, "_ref", "libref_cpu_strict.so" if strict else "libref_cpu.so"))
 
 
+def ref_gpu_lib():
+    """oracle/_ref/libref_gpu.so: the reference's unmodified GPU kernels (src/laplacian_gpu.hpp,
+    src/geometry_gpu.hpp) recompiled for sm_100a behind oracle/ref_gpu_shim.cu."""
+    return _load(os.path.join(_HERE, "_ref", "libref_gpu.so"))
+
+
 def port_lib():
     return _load(os.path.join(_HERE, "libport.so"))
 
@@ -78,3 +84,24 @@ def port_geometry(lib, nq, xgeom, geometry_dofmap, dphi, weights, cells):
     fn(C.c_int(nq), _p(xgeom), _p(G), _p(geometry_dofmap), _p(dphi), _p(weights), _p(cells),
        C.c_int(len(cells)))
     return G
+
+
+def ref_gpu_stiffness(lib, degree, nq, identity, u, y, G, constants, phi0, dphi1, cell_dofmap, cells, ncells,
+                      bc_marker, bits):
+    """Launch stiffness_operator_gpu<T,P,Q> (src/laplacian_gpu.hpp:91-426) with the reference's launch
+    shape; every array argument is a device pointer (int); y += A u on the default stream."""
+    rc = lib.ref_stiffness_operator_gpu(
+        C.c_int(bits), C.c_int(degree), C.c_int(nq), C.c_void_p(u), C.c_void_p(constants), C.c_void_p(y),
+        C.c_void_p(G), C.c_void_p(phi0), C.c_void_p(dphi1), C.c_void_p(cell_dofmap), C.c_void_p(cells),
+        C.c_int(ncells), C.c_void_p(bc_marker), C.c_int(int(identity)))
+    if rc != 0:
+        raise RuntimeError(f"reference GPU stiffness kernel failed with {rc}")
+
+
+def ref_gpu_geometry(lib, nq, xgeom, G, geometry_dofmap, dphi, weights, cells, ncells, bits):
+    """Launch geometry_computation_gpu<T,Q> (src/geometry_gpu.hpp:26-132); device pointers."""
+    rc = lib.ref_geometry_computation_gpu(
+        C.c_int(bits), C.c_int(nq), C.c_void_p(xgeom), C.c_void_p(G), C.c_void_p(geometry_dofmap),
+        C.c_void_p(dphi), C.c_void_p(weights), C.c_void_p(cells), C.c_int(ncells))
+    if rc != 0:
+        raise RuntimeError(f"reference GPU geometry kernel failed with {rc}")
