@@ -269,6 +269,14 @@ class Halo:
             check(lib.bd_halo_create(comm._h, bits, mesh.ndofs_owned, mesh.nghost, len(sr), _ptr(sr),
                                      _ptr(sc), _ptr(si), len(rr), _ptr(rr), _ptr(rc), C.byref(self._h)))
 
+    def set_unpack(self, ghost_positions):
+        """Message entry i lands at ghost position ghost_positions[i] (ghosts in arbitrary order)."""
+        if ghost_positions is None:
+            check(lib.bd_halo_set_unpack(self._h, None))
+        else:
+            gp = np.ascontiguousarray(ghost_positions, dtype=np.int32)
+            check(lib.bd_halo_set_unpack(self._h, _ptr(gp)))
+
     def begin(self, x, stream=None):
         check(lib.bd_halo_begin(self._h, x.data_ptr(), _stream_ptr(stream)))
 

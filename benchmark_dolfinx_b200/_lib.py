@@ -96,6 +96,7 @@ PROTOTYPES = {
     "bd_comm_destroy": (C.c_int, [_V]),
     "bd_halo_create": (C.c_int, [_V, C.c_int, C.c_int64, C.c_int64, C.c_int, _V, _V, _V, C.c_int, _V,
                                  _V, C.POINTER(_V)]),
+    "bd_halo_set_unpack": (C.c_int, [_V, _V]),
     "bd_halo_destroy": (C.c_int, [_V]),
     "bd_halo_begin": (C.c_int, [_V, _V, _V]),
     "bd_halo_end": (C.c_int, [_V, _V]),

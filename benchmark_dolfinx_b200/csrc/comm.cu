@@ -221,6 +221,23 @@ extern "C" int bd_halo_create(bd_comm* comm, int scalar_bits, int64_t n_owned, i
   return BD_SUCCESS;
 }
 
+extern "C" int bd_halo_set_unpack(bd_halo* h, const int32_t* ghost_positions_host)
+{
+  BD_REQUIRE(h, "bd_halo_set_unpack: null plan");
+  if (!ghost_positions_host)
+  {
+    h->use_unpack = false;
+    return BD_SUCCESS;
+  }
+  for (std::int64_t i = 0; i < h->n_ghost; ++i)
+    if (ghost_positions_host[i] < 0 || ghost_positions_host[i] >= h->n_ghost)
+      return fail(BD_ERR_INVALID_ARGUMENT, "ghost position %lld out of range", (long long)i);
+  BD_CHECK(h->unpack_idx.assign(ghost_positions_host, static_cast<size_t>(h->n_ghost), false));
+  BD_CHECK(h->recv_buf.alloc(static_cast<size_t>(h->n_ghost > 0 ? h->n_ghost : 1) * (h->scalar_bits / 8)));
+  h->use_unpack = true;
+  return BD_SUCCESS;
+}
+
 extern "C" int bd_halo_destroy(bd_halo* h)
 {
   if (!h)
@@ -257,7 +274,8 @@ extern "C" int bd_halo_begin(bd_halo* h, void* x_dev, void* stream_)
                              h->send_ranks[i], nc, h->stream));
       off += h->send_counts[i];
     }
-    char* ghost = static_cast<char*>(x_dev) + static_cast<size_t>(h->n_owned) * ts;
+    char* ghost_seg = static_cast<char*>(x_dev) + static_cast<size_t>(h->n_owned) * ts;
+    char* ghost = h->use_unpack ? h->recv_buf.ptr : ghost_seg;
     off = 0;
     for (size_t i = 0; i < h->recv_ranks.size(); ++i)
     {
@@ -266,6 +284,8 @@ extern "C" int bd_halo_begin(bd_halo* h, void* x_dev, void* stream_)
       off += h->recv_counts[i];
     }
     BD_NCCL_CHECK(api.GroupEnd());
+    if (h->use_unpack)
+      BD_CHECK(bd_unpack(h->scalar_bits, h->n_ghost, h->unpack_idx.ptr, h->recv_buf.ptr, ghost_seg, h->stream));
   }
   BD_CUDA_CHECK(cudaEventRecord(h->ev_done, h->stream));
   return BD_SUCCESS;

@@ -22,6 +22,11 @@ struct bd_halo
   std::int64_t n_send_total = 0;
   bd::DeviceArray<std::int32_t> send_idx;
   bd::DeviceArray<char> send_buf;
+  // optional unpack (ghosts not ordered by source rank): receive into recv_buf, then
+  // x[n_owned + unpack_idx[i]] = recv_buf[i]  (unpack_gpu, reference src/vector.hpp:52-62)
+  bd::DeviceArray<std::int32_t> unpack_idx;
+  bd::DeviceArray<char> recv_buf;
+  bool use_unpack = false;
   cudaStream_t stream = nullptr;      // exchange runs here, overlapped with the lcells kernel
   cudaEvent_t ev_ready = nullptr;     // producer of x done
   cudaEvent_t ev_done = nullptr;      // ghosts of x up to date

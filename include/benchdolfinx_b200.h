@@ -207,6 +207,11 @@ int bd_halo_create(bd_comm* comm, int scalar_bits, int64_t n_owned, int64_t n_gh
                    const int32_t* send_ranks, const int64_t* send_counts,
                    const int32_t* send_indices_host, int n_recv, const int32_t* recv_ranks,
                    const int64_t* recv_counts, bd_halo** out);
+/* For ghost segments that are NOT ordered by source rank (DOLFINx makes no such promise): message
+ * entry i (messages concatenated in recv_ranks order) belongs at ghost position ghost_positions[i];
+ * the plan then receives into an internal buffer and scatters with the unpack kernel (unpack_gpu,
+ * src/vector.hpp:52-62, get_unpack_fn :125-149).  NULL switches back to in-place receives. */
+int bd_halo_set_unpack(bd_halo* halo, const int32_t* ghost_positions_host);
 int bd_halo_destroy(bd_halo* halo);
 /* x[n_owned:] <- owners' values.  begin: pack + post sends/receives on the plan's
  * own stream after the work already queued on `stream`; end: make `stream` wait. */

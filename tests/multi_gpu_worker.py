@@ -39,6 +39,23 @@ def main():
                         unorm_ref=unorm, ynorm_ref=ynorm))
         assert abs(res.unorm - unorm) <= 1e-12 * unorm, (rank, out[-1])
         assert abs(res.ynorm - ynorm) <= 1e-11 * ynorm, (rank, out[-1])
+    # ghosts in scrambled order: the same exchange through the unpack path (bd_halo_set_unpack)
+    import numpy as np
+    mesh = bd.BoxMesh(bd.compute_mesh_size(20000, 3), 3, rank, world)
+    halo = bd.Halo(comm, mesh)
+    x = torch.zeros(mesh.ndofs_local, dtype=torch.float64, device="cuda")
+    x[:mesh.ndofs_owned] = torch.arange(mesh.ndofs_owned, dtype=torch.float64, device="cuda") + 1000.0 * rank
+    ref = x.clone()
+    halo.scatter_fwd(ref)
+    perm = np.random.default_rng(rank).permutation(mesh.nghost).astype(np.int32)
+    halo.set_unpack(perm)
+    y = x.clone()
+    halo.scatter_fwd(y)
+    torch.cuda.synchronize()
+    expect = ref.clone()
+    expect[mesh.ndofs_owned + torch.from_numpy(perm.astype(np.int64)).cuda()] = ref[mesh.ndofs_owned:]
+    assert torch.equal(y, expect), rank
+    halo.set_unpack(None)
     if rank == 0:
         print("MULTI_GPU_CHECK " + json.dumps(out), flush=True)
     dist.destroy_process_group()
