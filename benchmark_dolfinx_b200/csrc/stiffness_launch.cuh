@@ -99,7 +99,7 @@ struct SlabTmaTuning
   static constexpr int NSTAGE = NQ <= 5 ? 2 : (NQ == 6 ? 3 : 4);
   static constexpr int Q0C = NQ <= 5 ? NQ : (NQ == 6 ? 3 : (NQ == 8 ? 2 : (NQ == 9 ? 3 : NQ)));
   static constexpr int WARPS = 1;
-  static constexpr bool PREFETCH = NQ <= 5;
+  static constexpr bool PREFETCH = NQ <= 5; // also nq = 6 with nd = 5 (see launch_stiffness_slab_tma)
 };
 
 // Slab kernel with the G stream on asynchronous bulk copies (stiffness_slab.cuh), explicit tuning.
@@ -156,7 +156,9 @@ int launch_stiffness_slab_tma(const StiffnessArgs& a)
     if (slab_tune_variant() == 1)
       return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, 3, NQ, 2, true>(a);
   }
-  return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, NSTAGE, TU::Q0C, TU::WARPS, TU::PREFETCH>(a);
+  // the gather prefetch needs 3 * nd^2 extra registers: affordable up to nd = 5
+  constexpr bool PF = TU::PREFETCH || (NQ == 6 && P + 1 <= 5);
+  return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, NSTAGE, TU::Q0C, TU::WARPS, PF>(a);
 }
 
 template <typename T, int P, int NQ>

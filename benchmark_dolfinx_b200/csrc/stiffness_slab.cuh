@@ -180,6 +180,11 @@ __device__ __forceinline__ void slab_forward_x(const SlabTables<T, ND, NQ>& tab,
 // rows it needs are fetched from the constant bank with a warp-uniform dynamic index.  Fully unrolled,
 // these phases are ~10k instructions each at ND = 8 and ncu shows the warps starving on instruction
 // fetch ("no instruction" = 3.4 of 7 stall cycles per issue) on top of register spills.
+#ifndef BD_SLAB_ROLLED_FROM_NQ
+#define BD_SLAB_ROLLED_FROM_NQ 6
+#endif
+constexpr int kSlabRolledFromNQ = BD_SLAB_ROLLED_FROM_NQ; // rolled X phases from this nq on
+
 template <typename T, int ND, int NQ, int RL, int CUBE>
 __device__ __forceinline__ void slab_forward_x_rolled(const SlabTables<T, ND, NQ>& tab, const T (&ul)[ND * ND],
                                                       T* __restrict__ dst0)
@@ -752,7 +757,7 @@ __global__ void __launch_bounds__(WARPS_ * 32)
         }
         ul[t] *= kappa; // kappa folded into the input: y = A(kappa) u = A(1) (kappa u)
       }
-      if constexpr (NQ >= 9 && !IDENTITY)
+      if constexpr (NQ >= kSlabRolledFromNQ && !IDENTITY)
         slab_forward_x_rolled<T, ND, NQ, RL, CUBE>(tab, ul, cube + m * RL + rbase);
       else
         slab_forward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, ul, cube + m * RL + rbase);
@@ -833,7 +838,7 @@ __global__ void __launch_bounds__(WARPS_ * 32)
     if (xlane)
     {
       T out[ND2];
-      if constexpr (NQ >= 9 && !IDENTITY)
+      if constexpr (NQ >= kSlabRolledFromNQ && !IDENTITY)
         slab_backward_x_rolled<T, ND, NQ, RL, CUBE>(tab, cube + m * RL + rbase, out);
       else
         slab_backward_x<T, ND, NQ, RL, CUBE, IDENTITY>(tab, cube + m * RL + rbase, out);
