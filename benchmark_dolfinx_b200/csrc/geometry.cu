@@ -145,6 +145,12 @@ int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std:
   if (ncells == 0)
     return BD_SUCCESS;
   const int grid = sm_count() * 8;
+  if (layout == 0)
+  {
+    const size_t bytes = static_cast<size_t>(ncells) * 6 * nq * nq * nq * (scalar_bits / 8);
+    BD_CUDA_CHECK(cudaMemcpyAsync(G, Gs, bytes, cudaMemcpyDeviceToDevice, stream));
+    return BD_SUCCESS;
+  }
   if (layout == 2)
   {
     if (scalar_bits == 64)

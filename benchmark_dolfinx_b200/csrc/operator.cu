@@ -122,7 +122,7 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
   // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272), written
   // straight into the layout the stiffness kernel streams; lcells and bcells are separate segments
   // because they are separate launches (the bcells pointer offset of src/laplacian.hpp:329).
-  op->g_layout = preferred_g_layout(op->scalar_bits, op->nq);
+  op->g_layout = preferred_g_layout(op->scalar_bits, op->degree, op->nq);
   op->g_bcells_offset = g_layout_size(op->g_layout, op->nq, op->n_lcells);
   const std::int64_t g_total = op->g_bcells_offset + g_layout_size(op->g_layout, op->nq, op->n_bcells);
   TRY(op->G.alloc(static_cast<size_t>(g_total > 0 ? g_total : 1) * ts));
@@ -239,6 +239,7 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
   BD_REQUIRE(op && buf && n > 0, "bd_laplacian_describe: null argument");
   const char* t = op->scalar_bits == 64 ? "double" : "float";
   const char* kernel = op->g_layout == 2 ? "bd::stiffness_mma8_kernel (fp64 DMMA m8n8k4 arithmetic, UBLKCP G ring)"
+                       : op->g_layout == 0 ? "bd::stiffness_pencil_kernel (register pencils, streamed G rows)"
                        : (stiffness_variant() == 1 ? "bd::stiffness_slab_kernel (register slabs, LDG G)"
                                                    : "bd::stiffness_slab_tma_kernel (register slabs, UBLKCP G ring)");
   snprintf(buf, n, "%s, T=%s, P=%d, nq=%d, G layout %d", kernel, t, op->degree, op->nq, op->g_layout);

@@ -36,7 +36,7 @@ struct bd_laplacian
   // G is stored in the slab layout (stiffness_slab.cuh): lcells segment, then bcells segment,
   // each rounded up to whole warp batches
   bool slab = true;
-  int g_layout = 1; // 1 slab, 2 DMMA accumulator order (see stiffness_launch.cuh)
+  int g_layout = 1; // 0 reference order (pencil kernel), 1 slab, 2 DMMA accumulator order (see stiffness_launch.cuh)
   std::int64_t g_bcells_offset = 0; // scalars before the bcells segment
   bd::DeviceArray<char> G_reference; // reference-layout copy, built on demand (bd_laplacian_geometry)
   std::int64_t g_cell_stride() const { return 6ll * nq * nq * nq; }

@@ -17,6 +17,8 @@ int stiffness_variant()
       return 1;
     if (!std::strcmp(e, "tma"))
       return 2;
+    if (!std::strcmp(e, "pencil"))
+      return 3;
     return 0;
   }();
   return v;
@@ -55,8 +57,20 @@ int slab_tune_variant()
   return v;
 }
 
-int preferred_g_layout(int scalar_bits, int nq)
+int pencil_cpb_variant()
 {
+  static const int v = [] {
+    const char* e = std::getenv("BD_PENCIL_CPB");
+    return e ? std::atoi(e) : 0;
+  }();
+  return v;
+}
+
+int preferred_g_layout(int scalar_bits, int degree, int nq)
+{
+  const bool pencil_built = nq == degree + 2 && nq >= 6; // pencil_instantiated() in stiffness_launch.cuh
+  if (pencil_built && stiffness_variant() == 3)
+    return 0;
   if ((nq == 8 || nq == 7) && stiffness_variant() != 1)
     return 2;
   return 1;

@@ -13,13 +13,15 @@ namespace bd
 #if BD_INST_QMODE == 0
 #define BD_CASE(P)                                                                                 \
   case P:                                                                                          \
-    return a.slab ? launch_stiffness_slab<BD_INST_T, P, P + 1, true>(a)                            \
-                  : launch_stiffness<BD_INST_T, P, P + 1, true>(a);
+    return !a.slab ? launch_stiffness<BD_INST_T, P, P + 1, true>(a)                                \
+           : a.g_layout == 0 ? launch_stiffness_pencil<BD_INST_T, P, P + 1, true>(a)               \
+                             : launch_stiffness_slab<BD_INST_T, P, P + 1, true>(a);
 #else
 #define BD_CASE(P)                                                                                 \
   case P:                                                                                          \
-    return a.slab ? launch_stiffness_slab<BD_INST_T, P, P + 2, false>(a)                           \
-                  : launch_stiffness<BD_INST_T, P, P + 2, false>(a);
+    return !a.slab ? launch_stiffness<BD_INST_T, P, P + 2, false>(a)                               \
+           : a.g_layout == 0 ? launch_stiffness_pencil<BD_INST_T, P, P + 2, false>(a)              \
+                             : launch_stiffness_slab<BD_INST_T, P, P + 2, false>(a);
 #endif
 
 int BD_CAT(launch_stiffness_, BD_INST_SUFFIX, BD_INST_QMODE)(int degree, const StiffnessArgs& a)

@@ -4,11 +4,14 @@
 #include "common.cuh"
 #include "stiffness.cuh"
 #include "stiffness_slab.cuh"
+#include "stiffness_pencil.cuh"
 
 namespace bd
 {
-// 0 = default choice, 1 = plain slab kernel, 2 = asynchronous-copy slab kernel (env BD_STIFFNESS_VARIANT)
+// 0 = default choice, 1 = plain slab kernel, 2 = asynchronous-copy slab kernel, 3 = pencil kernel wherever
+// it is instantiated (env BD_STIFFNESS_VARIANT = slab | tma | pencil)
 int stiffness_variant();
+int pencil_cpb_variant(); // env BD_PENCIL_CPB: 0 = default cells per CTA, 1 = the alternative
 
 struct StiffnessArgs
 {
@@ -215,6 +218,69 @@ int launch_stiffness_slab(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
+// The pencil kernel (stiffness_pencil.cuh) is instantiated for qmode 1 with nq >= 6.
+template <int NQ, bool IDENTITY>
+constexpr bool pencil_instantiated()
+{
+  return !IDENTITY && NQ >= 6;
+}
+constexpr int pencil_alt_cpb(int nq)
+{
+  return nq >= 9 ? 3 : (nq == 8 ? 4 : (nq == 7 ? 2 : 3));
+}
+
+template <typename T, int P, int NQ, int CPB>
+int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
+{
+  using C = PencilConfig<T, P, NQ, CPB>;
+  static_assert(C::SUPPORTED, "pencil kernel: shared memory or CTA size out of range");
+  static_assert((C::ND - 1) * C::S1J + NQ <= C::S1I, "pencil kernel: S1 rows overlap");
+  constexpr int ND = P + 1;
+  auto kernel = stiffness_pencil_kernel<T, P, NQ, CPB>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, C::THREADS, C::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  SlabTables<T, ND, NQ> tab;
+  fill_slab_tables<T, ND, NQ, false>(tab, a.phi0_host, a.dphi1_host);
+  const std::int64_t nbatches = (a.ncells + CPB - 1) / CPB;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(nbatches < max_grid ? nbatches : max_grid);
+  kernel<<<grid, C::THREADS, C::CTA_SMEM, a.stream>>>(
+      static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
+      static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+// `a.G` in the reference layout (g_layout 0), `a.mdofmap` required.
+template <typename T, int P, int NQ, bool IDENTITY>
+int launch_stiffness_pencil(const StiffnessArgs& a)
+{
+  if constexpr (!pencil_instantiated<NQ, IDENTITY>())
+    return fail(BD_ERR_UNSUPPORTED, "the pencil kernel is not built for degree %d, nq %d", P, NQ);
+  else
+  {
+    if (a.ncells == 0)
+      return BD_SUCCESS;
+    if (a.ncells > 0x7fffffffLL)
+      return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+    if (!a.mdofmap)
+      return fail(BD_ERR_INVALID_ARGUMENT, "the pencil kernel needs the masked dofmap");
+    if (pencil_cpb_variant() == 1)
+      return launch_stiffness_pencil_cfg<T, P, NQ, pencil_alt_cpb(NQ)>(a);
+    return launch_stiffness_pencil_cfg<T, P, NQ, pencil_default_cpb(NQ)>(a);
+  }
+}
+
 // One function per (scalar, qmode), each defined in its own translation unit so
 // the 28 kernel instantiations compile in parallel.
 int launch_stiffness_f64_q0(int degree, const StiffnessArgs& a);
@@ -223,15 +289,15 @@ int launch_stiffness_f32_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_f32_q1(int degree, const StiffnessArgs& a);
 
 // in geometry.cu
-// G layouts: 0 = reference [cell][6][nq^3], 1 = slab (stiffness_slab.cuh), 2 = DMMA accumulator
-// order (stiffness_mma8.cuh; nq = 8)
+// G layouts: 0 = reference [cell][6][nq^3] (pencil kernel), 1 = slab (stiffness_slab.cuh), 2 = DMMA
+// accumulator order (stiffness_mma8.cuh; nq = 7, 8)
 int geometry_compute_layout(int scalar_bits, int nq, const void* xgeom, const std::int32_t* gdofmap,
                             const void* dphi, const void* weights, const std::int32_t* cells,
                             std::int64_t ncells, void* G, cudaStream_t stream, int layout);
 int layout_g_to_reference(int scalar_bits, int nq, const void* Gs, void* G, std::int64_t ncells,
                           cudaStream_t stream, int layout);
 // Layout the operator should use for (scalar_bits, nq) and the scalars it needs for ncells cells.
-int preferred_g_layout(int scalar_bits, int nq);
+int preferred_g_layout(int scalar_bits, int degree, int nq);
 std::int64_t g_layout_size(int layout, int nq, std::int64_t ncells);
 // in stiffness_mma8.cu
 int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const StiffnessArgs& a);

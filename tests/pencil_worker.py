@@ -1,0 +1,52 @@
+"""Run with BD_STIFFNESS_VARIANT=pencil (and optionally BD_PENCIL_CPB=1): parity of the pencil kernel with
+the oracle.  The variant is latched at the first operator call of a process, hence the separate process.
+Prints one JSON line per case; exit code 0 iff every case is within tolerance."""
+import json
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from oracle.boxmesh import compute_mesh_size, create_box_mesh  # noqa: E402
+from oracle.laplacian import OracleLaplacian  # noqa: E402
+from oracle.tables import Tables as OracleTables  # noqa: E402
+
+RTOL = {"f64": 1e-12, "f32": 1e-5}
+
+
+def main():
+    import torch
+    import benchmark_dolfinx_b200 as bd
+    ok = True
+    # (degree, ndofs): small meshes + one per degree with more batches than resident CTAs, so that the
+    # persistent loop, the dof prefetch and a ragged last batch are all exercised
+    cases = [(4, 4000), (5, 4000), (6, 4000), (7, 4000), (4, 400000), (5, 300000), (6, 300000), (7, 450000)]
+    for degree, ndofs in cases:
+        mesh = create_box_mesh(compute_mesh_size(ndofs, degree), degree, geom_perturb_fact=0.2)
+        oracle = OracleLaplacian(mesh, OracleTables(degree, 1), kappa=2.0, dtype=np.float64)
+        rng = np.random.default_rng(degree * 1000 + 7)
+        u = rng.uniform(-1, 1, mesh.ndofs_local)
+        y_ref = oracle.apply(u.copy())
+        for name, dtype in (("f64", np.float64), ("f32", np.float32)):
+            op = bd.MatFreeLaplacianGPU(mesh, degree, 1, 2.0, dtype=dtype)
+            desc = op.describe()
+            ud = torch.from_numpy(u.astype(dtype)).cuda()
+            yd = torch.full_like(ud, 7.0)
+            errs = []
+            for _ in range(2):  # twice: the second call starts from a used ring / used buffers
+                op.apply(ud, yd)
+                torch.cuda.synchronize()
+                y = yd.cpu().numpy().astype(np.float64)
+                errs.append(float(np.linalg.norm(y - y_ref) / np.linalg.norm(y_ref)))
+            g_err = float(np.linalg.norm(op.geometry().astype(np.float64) - oracle.G) / np.linalg.norm(oracle.G))
+            good = max(errs) < RTOL[name] and g_err < RTOL[name] and "pencil" in desc
+            ok = ok and good
+            print(json.dumps({"degree": degree, "ndofs": int(mesh.ndofs_local), "ncells": int(mesh.ncells),
+                              "dtype": name, "err": errs, "g_err": g_err, "kernel": desc, "ok": good}), flush=True)
+    return 0 if ok else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
