@@ -57,10 +57,10 @@ int slab_tune_variant()
   return v;
 }
 
-int pencil_cpb_variant()
+int pencil_ring_variant()
 {
   static const int v = [] {
-    const char* e = std::getenv("BD_PENCIL_CPB");
+    const char* e = std::getenv("BD_PENCIL_RING");
     return e ? std::atoi(e) : 0;
   }();
   return v;
@@ -68,8 +68,9 @@ int pencil_cpb_variant()
 
 int preferred_g_layout(int scalar_bits, int degree, int nq)
 {
-  const bool pencil_built = nq == degree + 2 && nq >= 6; // pencil_instantiated() in stiffness_launch.cuh
-  if (pencil_built && stiffness_variant() == 3)
+  // pencil kernel (reference layout): see pencil_instantiated() in stiffness_launch.cuh
+  const bool pencil = nq == degree + 2 && (nq == 9 || (scalar_bits == 32 && (nq == 7 || nq == 8)));
+  if (pencil && stiffness_variant() != 1 && stiffness_variant() != 2)
     return 0;
   if ((nq == 8 || nq == 7) && stiffness_variant() != 1)
     return 2;

@@ -11,7 +11,7 @@ namespace bd
 // 0 = default choice, 1 = plain slab kernel, 2 = asynchronous-copy slab kernel, 3 = pencil kernel wherever
 // it is instantiated (env BD_STIFFNESS_VARIANT = slab | tma | pencil)
 int stiffness_variant();
-int pencil_cpb_variant(); // env BD_PENCIL_CPB: 0 = default cells per CTA, 1 = the alternative
+int pencil_ring_variant(); // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead
 
 struct StiffnessArgs
 {
@@ -218,25 +218,22 @@ int launch_stiffness_slab(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
-// The pencil kernel (stiffness_pencil.cuh) is instantiated for qmode 1 with nq >= 6.
-template <int NQ, bool IDENTITY>
+// The pencil kernel (stiffness_pencil.cuh) is instantiated where it wins or is the only kernel without
+// spills (A/B in profiles/): qmode 1 with nq = 9, and fp32 with nq = 7, 8.
+template <typename T, int NQ, bool IDENTITY>
 constexpr bool pencil_instantiated()
 {
-  return !IDENTITY && NQ >= 6;
-}
-constexpr int pencil_alt_cpb(int nq)
-{
-  return nq >= 9 ? 3 : (nq == 8 ? 4 : (nq == 7 ? 2 : 3));
+  return !IDENTITY && (NQ == 9 || (sizeof(T) == 4 && (NQ == 7 || NQ == 8)));
 }
 
-template <typename T, int P, int NQ, int CPB>
+template <typename T, int P, int NQ, int CPB, int RD, bool UPF>
 int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
 {
-  using C = PencilConfig<T, P, NQ, CPB>;
+  using C = PencilConfig<T, P, NQ, CPB, RD>;
   static_assert(C::SUPPORTED, "pencil kernel: shared memory or CTA size out of range");
   static_assert((C::ND - 1) * C::S1J + NQ <= C::S1I, "pencil kernel: S1 rows overlap");
   constexpr int ND = P + 1;
-  auto kernel = stiffness_pencil_kernel<T, P, NQ, CPB>;
+  auto kernel = stiffness_pencil_kernel<T, P, NQ, CPB, RD, UPF>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -265,7 +262,7 @@ int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
 template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_pencil(const StiffnessArgs& a)
 {
-  if constexpr (!pencil_instantiated<NQ, IDENTITY>())
+  if constexpr (!pencil_instantiated<T, NQ, IDENTITY>())
     return fail(BD_ERR_UNSUPPORTED, "the pencil kernel is not built for degree %d, nq %d", P, NQ);
   else
   {
@@ -275,9 +272,16 @@ int launch_stiffness_pencil(const StiffnessArgs& a)
       return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
     if (!a.mdofmap)
       return fail(BD_ERR_INVALID_ARGUMENT, "the pencil kernel needs the masked dofmap");
-    if (pencil_cpb_variant() == 1)
-      return launch_stiffness_pencil_cfg<T, P, NQ, pencil_alt_cpb(NQ)>(a);
-    return launch_stiffness_pencil_cfg<T, P, NQ, pencil_default_cpb(NQ)>(a);
+    // One cell per CTA throughout (measured best for nq = 7, 8, 9).  fp32: G requested a whole cell
+    // ahead and the next cell's input prefetched; fp64: ring of 3 rows and no input prefetch, which keeps
+    // the kernel at <= 160 registers and 40 KB, i.e. 4 CTAs (12 warps) per SM.  BD_PENCIL_RING = 1 / 2
+    // forces the short / the full ring (experiments).
+    constexpr int FULL = NQ + 1;
+    const int ring = pencil_ring_variant();
+    const bool full = ring == 2 || (ring == 0 && sizeof(T) == 4);
+    if (full)
+      return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true>(a);
+    return launch_stiffness_pencil_cfg<T, P, NQ, 1, 3, false>(a);
   }
 }
 

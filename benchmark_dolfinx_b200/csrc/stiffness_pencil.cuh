@@ -25,8 +25,11 @@
 //
 // G is read in the reference layout [pos][comp][q0][q1][q2] (src/geometry_gpu.hpp:24-119): every
 // thread copies the six entries of its own point of a q0 row with cp.async (L2 evict-first hint)
-// into a private slot of a small shared-memory ring, RD - 1 rows ahead of their use; nobody else
-// reads the slot, so the ring needs no barrier, only cp.async.wait_group.
+// into a private slot of a shared-memory ring of RD rows, RD - 1 rows ahead of their use.  The rows
+// of all the cells a CTA visits form one stream, so with RD = NQ + 1 a row is requested a whole
+// cell before it is needed (while the previous cell is still in phase 3) and the HBM latency is
+// covered by phases 4, 5, 1 and 2.  Nobody else reads a thread's slots: the ring needs no barrier,
+// only cp.async.wait_group.
 //
 // fp64: the outer loop of every phase is rolled.  DFMA cannot take a constant-bank operand on
 // sm_100 (the table entry comes through a uniform register, one LDCU per use); fully unrolled, the
@@ -75,18 +78,10 @@ constexpr PencilStrides pencil_s1_strides(int nd, int nq, bool is_double)
   return {nd * b, b};
 }
 
-// Cells per CTA: fill the warps of a 96..256-thread CTA as completely as possible.
-constexpr int pencil_default_cpb(int nq)
-{
-  return nq >= 9 ? 1 : (nq == 8 ? 2 : (nq == 7 ? 5 : (nq == 6 ? 7 : (256 / (nq * nq)))));
-}
-
-constexpr int kPencilRing = 3; // q0 rows of G in flight per cell
-
-template <typename T, int P, int NQ, int CPB>
+template <typename T, int P, int NQ, int CPB, int RD_>
 struct PencilConfig
 {
-  static constexpr int RD = kPencilRing;
+  static constexpr int RD = RD_; // rows of G in the ring (2 .. NQ + 1)
   static constexpr int ND = P + 1;
   static constexpr int TPC = NQ * NQ; // threads per cell
   static constexpr int THREADS = (CPB * TPC + 31) / 32 * 32;
@@ -102,20 +97,20 @@ struct PencilConfig
   static constexpr int RING = RD * 6 * TPC; // G ring: [slot][comp][qy*NQ + qz]
   static constexpr int CELL_SCALARS = (2 * S1V + 3 * S2V + RING + 3) / 4 * 4;
   static constexpr int CTA_SMEM = CPB * CELL_SCALARS * int(sizeof(T));
-  static constexpr bool SUPPORTED = CTA_SMEM <= 226 * 1024 && THREADS <= 1024;
+  static constexpr bool SUPPORTED = CTA_SMEM <= 226 * 1024 && THREADS <= 1024 && RD >= 2 && RD <= NQ + 1;
 };
 
 // One G entry (read once per operator application: evict-first in L2) from global to shared memory.
 template <typename T>
-__device__ __forceinline__ void cp_async_scalar(T* dst, const T* src, std::uint64_t policy)
+__device__ __forceinline__ void cp_async_scalar(std::uint32_t dst_smem, const T* src, std::uint64_t policy)
 {
   static_assert(sizeof(T) == 4 || sizeof(T) == 8, "cp.async.ca copies 4, 8 or 16 bytes");
   if constexpr (sizeof(T) == 8)
-    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 8, %2;" ::"r"(smem_addr(dst)), "l"(src),
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 8, %2;" ::"r"(dst_smem), "l"(src),
                  "l"(policy)
                  : "memory");
   else
-    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;" ::"r"(smem_addr(dst)), "l"(src),
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;" ::"r"(dst_smem), "l"(src),
                  "l"(policy)
                  : "memory");
 }
@@ -163,19 +158,57 @@ __device__ __forceinline__ void pencil_load_dofs(const std::int32_t* row, std::i
   }
 }
 
-template <typename T, int P, int NQ, int CPB>
-__global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
+// sum_k row[k] * v[k].  fp64: two partial sums -- the rolled loops leave only a few independent DFMA
+// chains per warp, and with 9-12 warps per SM their latency shows (ncu: "wait" is the top stall).
+template <typename T, int N>
+__device__ __forceinline__ T pencil_dot(const T* __restrict__ row, const T (&v)[N])
+{
+  if constexpr (sizeof(T) == 8 && N >= 4)
+  {
+    T s0 = row[0] * v[0], s1 = row[1] * v[1];
+#pragma unroll
+    for (int k = 2; k + 1 < N; k += 2)
+    {
+      s0 += row[k] * v[k];
+      s1 += row[k + 1] * v[k + 1];
+    }
+    if constexpr (N % 2 == 1)
+      s0 += row[N - 1] * v[N - 1];
+    return s0 + s1;
+  }
+  else
+  {
+    T s = 0;
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+      s += row[k] * v[k];
+    return s;
+  }
+}
+
+// fp64: ask for 4 CTAs per SM when the CTA is one cell of nq = 9 (96 threads): 12 warps, <= 168 registers
+template <typename T, int P, int NQ, int CPB, int RD>
+constexpr int pencil_min_ctas()
+{
+  return (sizeof(T) == 8 && PencilConfig<T, P, NQ, CPB, RD>::THREADS <= 96
+          && 4 * PencilConfig<T, P, NQ, CPB, RD>::CTA_SMEM <= 220 * 1024)
+             ? 4
+             : 1;
+}
+
+template <typename T, int P, int NQ, int CPB, int RD, bool UPF>
+__global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, pencil_min_ctas<T, P, NQ, CPB, RD>())
     stiffness_pencil_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ G,
                             const T* __restrict__ cell_constants,
                             const std::int32_t* __restrict__ mdofmap,
                             const std::int32_t* __restrict__ cells, int ncells,
                             const __grid_constant__ SlabTables<T, P + 1, NQ> tab)
 {
-  using C = PencilConfig<T, P, NQ, CPB>;
+  using C = PencilConfig<T, P, NQ, CPB, RD>;
   constexpr int ND = C::ND, TPC = C::TPC, NQ3 = TPC * NQ, ND2 = ND * ND, ND3 = ND2 * ND;
-  constexpr int S1I = C::S1I, S1J = C::S1J, S1V = C::S1V, S2I = C::S2I, S2V = C::S2V, RD = C::RD;
+  constexpr int S1I = C::S1I, S1J = C::S1J, S1V = C::S1V, S2I = C::S2I, S2V = C::S2V;
   constexpr int OUTER = sizeof(T) == 8 ? 1 : NQ; // unroll factor of the outer loop of each phase
-  static_assert(RD >= 2 && RD <= NQ, "ring depth");
+  static_assert(RD >= 2 && RD <= NQ + 1, "ring depth");
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int tid = threadIdx.x;
@@ -195,6 +228,7 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
   T* const s2_col = S2 + i2 * S2I + z2;       // + v*S2V + qy*NQ
   T* const s2_own = S2 + rem;                 // + v*S2V + i*S2I   (phase 3: point (:, qy, qz))
   T* const ring = S2 + 3 * S2V + rem;         // + (slot*6 + comp)*TPC   (phase 3, private to the thread)
+  constexpr int SLOT = 6 * TPC;
 
   const int nbatches = (ncells + CPB - 1) / CPB;
   const std::uint64_t g_policy = l2_evict_first_policy();
@@ -205,8 +239,52 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
     return mdofmap + static_cast<std::int64_t>(cells[pos]) * ND3 + (i1 * ND + j1) * ND;
   };
 
+  // G rows: one stream over all the cells this thread visits; row g lives in slot g % RD
+  auto g_of = [&](int batch) -> const T* {
+    const int pos = batch * CPB + c;
+    if (!(slot_ok && batch < nbatches && pos < ncells))
+      return nullptr;
+    return G + static_cast<std::int64_t>(pos) * (6 * NQ3) + rem;
+  };
+  // The destination is a per-thread shared-memory address in an ordinary register, advanced slot by
+  // slot.  (Derived from the rolled loop counter instead, ptxas 12.9 folds the slot offset into a
+  // uniform-register operand of LDGSTS next to the cache-hint descriptor and emits an encoding that
+  // faults -- seen for nd = 5, nq = 6 in fp64 -- hence the opaque asm in the rolled variant.)
+  constexpr std::uint32_t SLOT_BYTES = SLOT * sizeof(T);
+  const std::uint32_t ring_base = smem_addr(ring);
+  auto issue_row = [&](std::uint32_t dst, const T* gcell, int qx) {
+    const T* src = gcell + qx * TPC;
+#pragma unroll
+    for (int comp = 0; comp < 6; ++comp)
+      cp_async_scalar(dst + comp * TPC * std::uint32_t(sizeof(T)), src + comp * NQ3, g_policy);
+  };
+  std::uint32_t ring_wr = ring_base; // slot of the next row to request
+  const T* ring_rd = ring;           // slot of the next row to consume
+  const T* g_cur = g_of(blockIdx.x);
+  if (g_cur)
+  {
+    // rows 0 .. RD-2 of the first cell, one commit group per row
+#pragma unroll
+    for (int r = 0; r < RD - 1; ++r)
+    {
+      issue_row(ring_wr, g_cur, r);
+      cp_async_commit();
+      ring_wr += SLOT_BYTES;
+    }
+  }
+
   std::int32_t dof[ND];
-  pencil_load_dofs<ND>(row_of(blockIdx.x), dof);
+  T uv[ND];
+  {
+    const std::int32_t* row = row_of(blockIdx.x);
+    pencil_load_dofs<ND>(row, dof);
+    if constexpr (UPF)
+    {
+#pragma unroll
+      for (int k = 0; k < ND; ++k)
+        uv[k] = row ? u[dof[k] & 0x7fffffff] : T(0);
+    }
+  }
 
   for (int batch = blockIdx.x; batch < nbatches; batch += gridDim.x)
   {
@@ -214,36 +292,20 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
     const bool active = slot_ok && pos < ncells;
     const bool act1 = role1 && active;
     const bool act2 = role2 && active;
-    // next batch's dof row: its address is needed right after phase 1
+    // next batch: the address of its dof row is needed right after phase 1, its G rows in phase 3
     const std::int32_t* next_row = row_of(batch + gridDim.x);
-
-    // the first RD - 1 q0 rows of G travel while phases 1 and 2 run (one commit group per row)
-    const T* Gc = G + static_cast<std::int64_t>(active ? pos : 0) * (6 * NQ3) + rem;
-    auto issue_row = [&](int qx) {
-      T* dst = ring + (qx % RD) * (6 * TPC);
-      const T* src = Gc + qx * TPC;
-#pragma unroll
-      for (int comp = 0; comp < 6; ++comp)
-        cp_async_scalar(dst + comp * TPC, src + comp * NQ3, g_policy);
-    };
-    if (active)
-    {
-#pragma unroll
-      for (int r = 0; r < RD - 1; ++r)
-      {
-        issue_row(r);
-        cp_async_commit();
-      }
-    }
+    const T* g_next = g_of(batch + gridDim.x);
 
     // ---- phase 1: gather, BC masking (reference :153-170), z contraction
     if (act1)
     {
       const T kappa = cell_constants[pos];
-      T uv[ND];
+      if constexpr (!UPF)
+      {
 #pragma unroll
-      for (int k = 0; k < ND; ++k)
-        uv[k] = u[dof[k] & 0x7fffffff];
+        for (int k = 0; k < ND; ++k)
+          uv[k] = u[dof[k] & 0x7fffffff];
+      }
 #pragma unroll
       for (int k = 0; k < ND; ++k)
       {
@@ -257,15 +319,8 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
 #pragma unroll OUTER
       for (int qz = 0; qz < NQ; ++qz)
       {
-        T pz = 0, dz = 0;
-#pragma unroll
-        for (int k = 0; k < ND; ++k)
-        {
-          pz += tab.phi[qz * ND + k] * uv[k];
-          dz += tab.dphi[qz * ND + k] * uv[k];
-        }
-        s1_own[qz] = pz;
-        s1_own[S1V + qz] = dz;
+        s1_own[qz] = pencil_dot<T, ND>(tab.phi + qz * ND, uv);
+        s1_own[S1V + qz] = pencil_dot<T, ND>(tab.dphi + qz * ND, uv);
       }
     }
     std::int32_t ndof[ND];
@@ -285,17 +340,9 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
 #pragma unroll OUTER
       for (int qy = 0; qy < NQ; ++qy)
       {
-        T a = 0, b = 0, cz = 0;
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
-        {
-          a += tab.phi[qy * ND + j] * pzv[j];
-          b += tab.dphi[qy * ND + j] * pzv[j];
-          cz += tab.phi[qy * ND + j] * dzv[j];
-        }
-        s2_col[qy * NQ] = a;
-        s2_col[S2V + qy * NQ] = b;
-        s2_col[2 * S2V + qy * NQ] = cz;
+        s2_col[qy * NQ] = pencil_dot<T, ND>(tab.phi + qy * ND, pzv);
+        s2_col[S2V + qy * NQ] = pencil_dot<T, ND>(tab.dphi + qy * ND, pzv);
+        s2_col[2 * S2V + qy * NQ] = pencil_dot<T, ND>(tab.phi + qy * ND, dzv);
       }
     }
     __syncthreads();
@@ -315,27 +362,27 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
 #pragma unroll OUTER
       for (int qx = 0; qx < NQ; ++qx)
       {
-        // RD - 1 + qx groups have been committed; row qx is group qx
+        // row g of the stream is commit group g, and RD - 1 + g groups have been committed so far
         cp_async_wait<RD - 2>();
-        const T* gr = ring + (qx % RD) * (6 * TPC);
-        const T G0 = gr[0], G1 = gr[TPC], G2 = gr[2 * TPC], G3 = gr[3 * TPC], G4 = gr[4 * TPC],
-                G5 = gr[5 * TPC];
-        T gx = 0, gy = 0, gz = 0;
-#pragma unroll
-        for (int i = 0; i < ND; ++i)
-        {
-          gx += tab.dphi[qx * ND + i] * A[i];
-          gy += tab.phi[qx * ND + i] * B[i];
-          gz += tab.phi[qx * ND + i] * Cz[i];
-        }
+        const T G0 = ring_rd[0], G1 = ring_rd[TPC], G2 = ring_rd[2 * TPC], G3 = ring_rd[3 * TPC],
+                G4 = ring_rd[4 * TPC], G5 = ring_rd[5 * TPC];
+        ring_rd = (ring_rd == ring + (RD - 1) * SLOT) ? ring : ring_rd + SLOT;
+        const T gx = pencil_dot<T, ND>(tab.dphi + qx * ND, A);
+        const T gy = pencil_dot<T, ND>(tab.phi + qx * ND, B);
+        const T gz = pencil_dot<T, ND>(tab.phi + qx * ND, Cz);
         const T fx = G0 * gx + G1 * gy + G2 * gz;
         const T fy = G1 * gx + G3 * gy + G4 * gz;
         const T fz = G2 * gx + G4 * gy + G5 * gz;
-        // refill the slot read in the previous iteration (its values have been consumed above: gx..fz
-        // depend on this iteration's loads, which were issued after them)
+        // request row g + RD - 1 (of this cell or of the next one) into the slot consumed in the
+        // previous iteration: its values went into last iteration's fx, fy, fz
+        if constexpr (OUTER == 1)
+          asm volatile("" : "+r"(ring_wr));
         if (qx + RD - 1 < NQ)
-          issue_row(qx + RD - 1);
+          issue_row(ring_wr, g_cur, qx + RD - 1);
+        else if (g_next)
+          issue_row(ring_wr, g_next, qx + RD - 1 - NQ);
         cp_async_commit(); // also when empty: keeps the group count uniform
+        ring_wr = (ring_wr == ring_base + (RD - 1) * SLOT_BYTES) ? ring_base : ring_wr + SLOT_BYTES;
 #pragma unroll
         for (int i = 0; i < ND; ++i)
         {
@@ -352,6 +399,14 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
         s2_own[S2V + i * S2I] = oB[i];
         s2_own[2 * S2V + i * S2I] = oC[i];
       }
+    }
+    // next cell's input values: in flight during phases 4 and 5 (registers are free again)
+    T nuv[UPF ? ND : 1];
+    if constexpr (UPF)
+    {
+#pragma unroll
+      for (int k = 0; k < ND; ++k)
+        nuv[k] = next_row ? u[ndof[k] & 0x7fffffff] : T(0);
     }
     __syncthreads();
 
@@ -411,7 +466,12 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB>::THREADS)
     // thread reaches after its phase 4 reads of S2.  The ring is private to the thread.
 #pragma unroll
     for (int k = 0; k < ND; ++k)
+    {
       dof[k] = ndof[k];
+      if constexpr (UPF)
+        uv[k] = nuv[k];
+    }
+    g_cur = g_next;
   }
 }
 } // namespace bd

@@ -1,6 +1,7 @@
-"""Run with BD_STIFFNESS_VARIANT=pencil (and optionally BD_PENCIL_CPB=1): parity of the pencil kernel with
-the oracle.  The variant is latched at the first operator call of a process, hence the separate process.
-Prints one JSON line per case; exit code 0 iff every case is within tolerance."""
+"""Parity of the pencil kernel with the oracle for one setting of BD_PENCIL_RING (latched at the first
+operator call of a process, hence the separate process).
+Usage: pencil_worker.py [degree].  Prints one JSON line per case; exit code 0 iff every case is within
+tolerance."""
 import json
 import os
 import sys
@@ -22,7 +23,9 @@ def main():
     ok = True
     # (degree, ndofs): small meshes + one per degree with more batches than resident CTAs, so that the
     # persistent loop, the dof prefetch and a ragged last batch are all exercised
-    cases = [(4, 4000), (5, 4000), (6, 4000), (7, 4000), (4, 400000), (5, 300000), (6, 300000), (7, 450000)]
+    cases = [(5, 4000), (6, 4000), (7, 4000), (5, 300000), (6, 300000), (7, 450000)]
+    if len(sys.argv) > 1:
+        cases = [cs for cs in cases if cs[0] == int(sys.argv[1])]
     for degree, ndofs in cases:
         mesh = create_box_mesh(compute_mesh_size(ndofs, degree), degree, geom_perturb_fact=0.2)
         oracle = OracleLaplacian(mesh, OracleTables(degree, 1), kappa=2.0, dtype=np.float64)
@@ -41,7 +44,9 @@ def main():
                 y = yd.cpu().numpy().astype(np.float64)
                 errs.append(float(np.linalg.norm(y - y_ref) / np.linalg.norm(y_ref)))
             g_err = float(np.linalg.norm(op.geometry().astype(np.float64) - oracle.G) / np.linalg.norm(oracle.G))
-            good = max(errs) < RTOL[name] and g_err < RTOL[name] and "pencil" in desc
+            # the operator picks the pencil kernel for nq = 9 and, in fp32, for nq = 7, 8 (qmode 1)
+            expect_pencil = degree == 7 or (name == "f32" and degree in (5, 6))
+            good = max(errs) < RTOL[name] and g_err < RTOL[name] and (("pencil" in desc) == expect_pencil)
             ok = ok and good
             print(json.dumps({"degree": degree, "ndofs": int(mesh.ndofs_local), "ncells": int(mesh.ncells),
                               "dtype": name, "err": errs, "g_err": g_err, "kernel": desc, "ok": good}), flush=True)

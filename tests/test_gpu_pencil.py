@@ -1,6 +1,6 @@
-"""The pencil kernel (csrc/stiffness_pencil.cuh) against the oracle, for both cells-per-CTA settings.
+"""The pencil kernel (csrc/stiffness_pencil.cuh) against the oracle, for the three G-ring settings.
 
-The kernel choice is latched per process (BD_STIFFNESS_VARIANT), so the cases run in a worker process."""
+The setting is latched per process (BD_PENCIL_RING), so the cases run in a worker process."""
 import json
 import os
 import subprocess
@@ -13,11 +13,13 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-@pytest.mark.parametrize("cpb", ["0", "1"])
-def test_pencil_kernel_matches_oracle(cpb):
-    env = dict(os.environ, BD_STIFFNESS_VARIANT="pencil", BD_PENCIL_CPB=cpb)
-    r = subprocess.run([sys.executable, os.path.join(HERE, "pencil_worker.py")], env=env, capture_output=True,
-                       text=True, timeout=900)
+@pytest.mark.parametrize("degree", [5, 6, 7])
+@pytest.mark.parametrize("ring", ["0", "1", "2"])
+def test_pencil_kernel_matches_oracle(ring, degree):
+    env = dict(os.environ, BD_PENCIL_RING=ring, CUDA_LAUNCH_BLOCKING="1")
+    env.pop("BD_STIFFNESS_VARIANT", None)
+    r = subprocess.run([sys.executable, os.path.join(HERE, "pencil_worker.py"), str(degree)], env=env,
+                       capture_output=True, text=True, timeout=900)
     lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
-    assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
-    assert len(lines) == 16 and all(l["ok"] for l in lines)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-1500:])
+    assert len(lines) == 4 and all(l["ok"] for l in lines)
