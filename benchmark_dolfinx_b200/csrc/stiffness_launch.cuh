@@ -226,14 +226,14 @@ constexpr bool pencil_instantiated()
   return !IDENTITY && (NQ == 9 || (sizeof(T) == 4 && (NQ == 7 || NQ == 8)));
 }
 
-template <typename T, int P, int NQ, int CPB, int RD, bool UPF>
+template <typename T, int P, int NQ, int CPB, int RD, bool UPF, bool STREAM>
 int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
 {
   using C = PencilConfig<T, P, NQ, CPB, RD>;
   static_assert(C::SUPPORTED, "pencil kernel: shared memory or CTA size out of range");
   static_assert((C::ND - 1) * C::S1J + NQ <= C::S1I, "pencil kernel: S1 rows overlap");
   constexpr int ND = P + 1;
-  auto kernel = stiffness_pencil_kernel<T, P, NQ, CPB, RD, UPF>;
+  auto kernel = stiffness_pencil_kernel<T, P, NQ, CPB, RD, UPF, STREAM>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -280,8 +280,8 @@ int launch_stiffness_pencil(const StiffnessArgs& a)
     const int ring = pencil_ring_variant();
     const bool full = ring == 2 || (ring == 0 && sizeof(T) == 4);
     if (full)
-      return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true>(a);
-    return launch_stiffness_pencil_cfg<T, P, NQ, 1, 3, false>(a);
+      return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true>(a);
+    return launch_stiffness_pencil_cfg<T, P, NQ, 1, 3, false, false>(a);
   }
 }
 

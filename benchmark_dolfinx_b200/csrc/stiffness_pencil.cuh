@@ -186,17 +186,23 @@ __device__ __forceinline__ T pencil_dot(const T* __restrict__ row, const T (&v)[
   }
 }
 
-// fp64: ask for 4 CTAs per SM when the CTA is one cell of nq = 9 (96 threads): 12 warps, <= 168 registers
+// Minimum CTAs per SM for __launch_bounds__.  Without it the compiler spends registers on scheduling
+// freedom and halves the occupancy.  fp64 (one cell of nq = 9, 96 threads): 4 CTAs = 12 warps, <= 168
+// registers; fp32: <= 128 registers, as far as shared memory lets that many CTAs in.
 template <typename T, int P, int NQ, int CPB, int RD>
 constexpr int pencil_min_ctas()
 {
-  return (sizeof(T) == 8 && PencilConfig<T, P, NQ, CPB, RD>::THREADS <= 96
-          && 4 * PencilConfig<T, P, NQ, CPB, RD>::CTA_SMEM <= 220 * 1024)
-             ? 4
-             : 1;
+  using C = PencilConfig<T, P, NQ, CPB, RD>;
+  const int by_regs = sizeof(T) == 8 ? 65536 / (168 * C::THREADS) : 65536 / (128 * C::THREADS);
+  const int by_smem = (220 * 1024) / (C::CTA_SMEM + 1024);
+  const int n = by_regs < by_smem ? by_regs : by_smem;
+  return n < 1 ? 1 : n;
 }
 
-template <typename T, int P, int NQ, int CPB, int RD, bool UPF>
+// STREAM: the G rows of consecutive cells form one stream through the ring (rows are requested across
+// the cell boundary); otherwise the ring restarts with every cell (rows 0 .. RD-2 requested at the top of
+// the cell), which needs fewer registers.
+template <typename T, int P, int NQ, int CPB, int RD, bool UPF, bool STREAM>
 __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, pencil_min_ctas<T, P, NQ, CPB, RD>())
     stiffness_pencil_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ G,
                             const T* __restrict__ cell_constants,
@@ -208,7 +214,7 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
   constexpr int ND = C::ND, TPC = C::TPC, NQ3 = TPC * NQ, ND2 = ND * ND, ND3 = ND2 * ND;
   constexpr int S1I = C::S1I, S1J = C::S1J, S1V = C::S1V, S2I = C::S2I, S2V = C::S2V;
   constexpr int OUTER = sizeof(T) == 8 ? 1 : NQ; // unroll factor of the outer loop of each phase
-  static_assert(RD >= 2 && RD <= NQ + 1, "ring depth");
+  static_assert(RD >= 2 && RD <= NQ + 1 && (STREAM || RD <= NQ), "ring depth");
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int tid = threadIdx.x;
@@ -261,7 +267,7 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
   std::uint32_t ring_wr = ring_base; // slot of the next row to request
   const T* ring_rd = ring;           // slot of the next row to consume
   const T* g_cur = g_of(blockIdx.x);
-  if (g_cur)
+  if (STREAM && g_cur)
   {
     // rows 0 .. RD-2 of the first cell, one commit group per row
 #pragma unroll
@@ -294,7 +300,23 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
     const bool act2 = role2 && active;
     // next batch: the address of its dof row is needed right after phase 1, its G rows in phase 3
     const std::int32_t* next_row = row_of(batch + gridDim.x);
-    const T* g_next = g_of(batch + gridDim.x);
+    const T* g_next = STREAM ? g_of(batch + gridDim.x) : nullptr;
+    if constexpr (!STREAM)
+    {
+      // ring restarted per cell: slot of row qx is qx % RD (static in the unrolled variant, derived
+      // from the loop counter in the rolled one -- tests/test_abi.py checks the SASS for the faulting
+      // LDGSTS form described above)
+      g_cur = g_of(batch);
+      if (g_cur)
+      {
+#pragma unroll
+        for (int r = 0; r < RD - 1; ++r)
+        {
+          issue_row(ring_base + r * SLOT_BYTES, g_cur, r);
+          cp_async_commit();
+        }
+      }
+    }
 
     // ---- phase 1: gather, BC masking (reference :153-170), z contraction
     if (act1)
@@ -364,9 +386,11 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
       {
         // row g of the stream is commit group g, and RD - 1 + g groups have been committed so far
         cp_async_wait<RD - 2>();
-        const T G0 = ring_rd[0], G1 = ring_rd[TPC], G2 = ring_rd[2 * TPC], G3 = ring_rd[3 * TPC],
-                G4 = ring_rd[4 * TPC], G5 = ring_rd[5 * TPC];
-        ring_rd = (ring_rd == ring + (RD - 1) * SLOT) ? ring : ring_rd + SLOT;
+        const T* gr = STREAM ? ring_rd : ring + (qx % RD) * SLOT;
+        const T G0 = gr[0], G1 = gr[TPC], G2 = gr[2 * TPC], G3 = gr[3 * TPC], G4 = gr[4 * TPC],
+                G5 = gr[5 * TPC];
+        if constexpr (STREAM)
+          ring_rd = (ring_rd == ring + (RD - 1) * SLOT) ? ring : ring_rd + SLOT;
         const T gx = pencil_dot<T, ND>(tab.dphi + qx * ND, A);
         const T gy = pencil_dot<T, ND>(tab.phi + qx * ND, B);
         const T gz = pencil_dot<T, ND>(tab.phi + qx * ND, Cz);
@@ -375,14 +399,19 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
         const T fz = G2 * gx + G4 * gy + G5 * gz;
         // request row g + RD - 1 (of this cell or of the next one) into the slot consumed in the
         // previous iteration: its values went into last iteration's fx, fy, fz
-        if constexpr (OUTER == 1)
-          asm volatile("" : "+r"(ring_wr));
-        if (qx + RD - 1 < NQ)
-          issue_row(ring_wr, g_cur, qx + RD - 1);
-        else if (g_next)
-          issue_row(ring_wr, g_next, qx + RD - 1 - NQ);
+        if constexpr (STREAM)
+        {
+          if constexpr (OUTER == 1)
+            asm volatile("" : "+r"(ring_wr));
+          if (qx + RD - 1 < NQ)
+            issue_row(ring_wr, g_cur, qx + RD - 1);
+          else if (g_next)
+            issue_row(ring_wr, g_next, qx + RD - 1 - NQ);
+          ring_wr = (ring_wr == ring_base + (RD - 1) * SLOT_BYTES) ? ring_base : ring_wr + SLOT_BYTES;
+        }
+        else if (qx + RD - 1 < NQ)
+          issue_row(ring_base + ((qx + RD - 1) % RD) * SLOT_BYTES, g_cur, qx + RD - 1);
         cp_async_commit(); // also when empty: keeps the group count uniform
-        ring_wr = (ring_wr == ring_base + (RD - 1) * SLOT_BYTES) ? ring_base : ring_wr + SLOT_BYTES;
 #pragma unroll
         for (int i = 0; i < ND; ++i)
         {
@@ -471,7 +500,8 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
       if constexpr (UPF)
         uv[k] = nuv[k];
     }
-    g_cur = g_next;
+    if constexpr (STREAM)
+      g_cur = g_next;
   }
 }
 } // namespace bd

@@ -17,6 +17,6 @@ for cfg in "7 300000000 64" "6 500000000 32" "7 300000000 32" "5 300000000 32"; 
   one default 0 $1 $2 $3
   one default 1 $1 $2 $3
   one default 2 $1 $2 $3
-done 2>&1 | grep RESULT | tee gpurun_out/pencil_ab2.txt
+done 2>&1 | grep RESULT | tee gpurun_out/pencil_ab3.txt
 timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -6 | cut -c1-400 | tee gpurun_out/final_pytest.txt
 timeout 120 python -c "import __graft_entry__ as g; g.smoke(); print('SMOKE OK')" 2>&1 | tail -3 | tee gpurun_out/final_smoke.txt

@@ -98,3 +98,19 @@ def test_argument_errors_mirror_the_reference():
     assert rc == -2 and b"Unsupported nq" in _lib.lib.bd_last_error()
     rc = _lib.lib.bd_stiffness_apply(16, 3, 4, 1, 1, 1, 1, 1, 1, 1, 1, 1, 5, 1, None)
     assert rc == -1 and b"Invalid float size" in _lib.lib.bd_last_error()
+
+
+def test_no_ldgsts_with_uniform_register_offset():
+    """ptxas 12.9 can fold a rolled-loop slot offset into a uniform-register operand of LDGSTS (cp.async
+    with an L2 cache hint) and emit `LDGSTS [R+UR0+imm], desc[UR1]`, which faults at run time (seen in
+    csrc/stiffness_pencil.cuh for nd = 5, nq = 6, fp64).  The shipped library must not contain that form."""
+    import shutil
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    from benchmark_dolfinx_b200 import _lib
+    sass = subprocess.run([cuobjdump, "-sass", _lib.LIB_PATH], capture_output=True, text=True, timeout=600).stdout
+    copies = [l for l in sass.splitlines() if "LDGSTS" in l]
+    assert copies, "expected cp.async copies in the pencil kernel"
+    bad = [l.strip() for l in copies if re.search(r"\[R\d+\+UR\d+", l)]
+    assert not bad, bad[:4]
