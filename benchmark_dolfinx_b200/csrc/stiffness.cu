@@ -66,6 +66,15 @@ int pencil_ring_variant()
   return v;
 }
 
+int pencil_paired_variant()
+{
+  static const int v = [] {
+    const char* e = std::getenv("BD_PENCIL_PAIRED");
+    return e ? std::atoi(e) : 0;
+  }();
+  return v;
+}
+
 int preferred_g_layout(int scalar_bits, int degree, int nq)
 {
   // pencil kernel (reference layout): see pencil_instantiated() in stiffness_launch.cuh

@@ -11,7 +11,8 @@ namespace bd
 // 0 = default choice, 1 = plain slab kernel, 2 = asynchronous-copy slab kernel, 3 = pencil kernel wherever
 // it is instantiated (env BD_STIFFNESS_VARIANT = slab | tma | pencil)
 int stiffness_variant();
-int pencil_ring_variant(); // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead
+int pencil_ring_variant();   // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead
+int pencil_paired_variant(); // env BD_PENCIL_PAIRED: 1 = FFMA2 contractions in fp32
 
 struct StiffnessArgs
 {
@@ -226,14 +227,14 @@ constexpr bool pencil_instantiated()
   return !IDENTITY && (NQ == 9 || (sizeof(T) == 4 && (NQ == 7 || NQ == 8)));
 }
 
-template <typename T, int P, int NQ, int CPB, int RD, bool UPF, bool STREAM>
+template <typename T, int P, int NQ, int CPB, int RD, bool UPF, bool STREAM, bool PAIRED>
 int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
 {
   using C = PencilConfig<T, P, NQ, CPB, RD>;
   static_assert(C::SUPPORTED, "pencil kernel: shared memory or CTA size out of range");
   static_assert((C::ND - 1) * C::S1J + NQ <= C::S1I, "pencil kernel: S1 rows overlap");
   constexpr int ND = P + 1;
-  auto kernel = stiffness_pencil_kernel<T, P, NQ, CPB, RD, UPF, STREAM>;
+  auto kernel = stiffness_pencil_kernel<T, P, NQ, CPB, RD, UPF, STREAM, PAIRED>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -251,9 +252,27 @@ int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
   const std::int64_t nbatches = (a.ncells + CPB - 1) / CPB;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
   const int grid = static_cast<int>(nbatches < max_grid ? nbatches : max_grid);
+  PencilPairTables<PAIRED ? ND : 1, PAIRED ? NQ : 1> ptab{};
+  if constexpr (PAIRED)
+  {
+    constexpr int NQP = (NQ + 1) / 2, NDP = (ND + 1) / 2;
+    auto at = [](const T* t, int q, int k) { return (q < NQ && k < ND) ? static_cast<float>(t[q * ND + k]) : 0.f; };
+    for (int k = 0; k < ND; ++k)
+      for (int qp = 0; qp < NQP; ++qp)
+      {
+        ptab.fphi[k * NQP + qp] = make_float2(at(tab.phi, 2 * qp, k), at(tab.phi, 2 * qp + 1, k));
+        ptab.fdphi[k * NQP + qp] = make_float2(at(tab.dphi, 2 * qp, k), at(tab.dphi, 2 * qp + 1, k));
+      }
+    for (int q = 0; q < NQ; ++q)
+      for (int kp = 0; kp < NDP; ++kp)
+      {
+        ptab.bphi[q * NDP + kp] = make_float2(at(tab.phi, q, 2 * kp), at(tab.phi, q, 2 * kp + 1));
+        ptab.bdphi[q * NDP + kp] = make_float2(at(tab.dphi, q, 2 * kp), at(tab.dphi, q, 2 * kp + 1));
+      }
+  }
   kernel<<<grid, C::THREADS, C::CTA_SMEM, a.stream>>>(
       static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
-      static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+      static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab, ptab);
   BD_CUDA_CHECK(cudaGetLastError());
   return BD_SUCCESS;
 }
@@ -279,9 +298,15 @@ int launch_stiffness_pencil(const StiffnessArgs& a)
     constexpr int FULL = NQ + 1;
     const int ring = pencil_ring_variant();
     const bool full = ring == 2 || (ring == 0 && sizeof(T) == 4);
+    if constexpr (sizeof(T) == 4)
+    {
+      // BD_PENCIL_PAIRED = 1: contractions on FFMA2 (experiment)
+      if (full && pencil_paired_variant() == 1)
+        return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true, true>(a);
+    }
     if (full)
-      return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true>(a);
-    return launch_stiffness_pencil_cfg<T, P, NQ, 1, 3, false, false>(a);
+      return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true, false>(a);
+    return launch_stiffness_pencil_cfg<T, P, NQ, 1, 3, false, false, false>(a);
   }
 }
 

@@ -158,6 +158,28 @@ __device__ __forceinline__ void pencil_load_dofs(const std::int32_t* row, std::i
   }
 }
 
+// fp32 tables for the FFMA2 variant (two fp32 FMAs per instruction: a scalar from a register times a
+// pair of table entries from a uniform register, added to a register pair).  Forward phases pair two
+// neighbouring quadrature points, backward phases two neighbouring dofs; odd extents are zero padded.
+template <int ND, int NQ>
+struct PencilPairTables
+{
+  static constexpr int NQP = (NQ + 1) / 2, NDP = (ND + 1) / 2;
+  float2 fphi[ND * NQP];  // [k][qp] = (Phi[2qp][k],  Phi[2qp+1][k])
+  float2 fdphi[ND * NQP]; // [k][qp] = (DPhi[2qp][k], DPhi[2qp+1][k])
+  float2 bphi[NQ * NDP];  // [q][kp] = (Phi[q][2kp],  Phi[q][2kp+1])
+  float2 bdphi[NQ * NDP]; // [q][kp] = (DPhi[q][2kp], DPhi[q][2kp+1])
+};
+__device__ __forceinline__ float2 pair_fma(float s, float2 t, float2 acc)
+{
+  return __ffma2_rn(make_float2(s, s), t, acc); // SASS: FFMA2 R, R.F32, UR.F32x2, R.F32x2
+}
+template <int N>
+__device__ __forceinline__ float pair_get(const float2 (&v)[N], int i)
+{
+  return (i & 1) ? v[i >> 1].y : v[i >> 1].x;
+}
+
 // sum_k row[k] * v[k].  fp64: two partial sums -- the rolled loops leave only a few independent DFMA
 // chains per warp, and with 9-12 warps per SM their latency shows (ncu: "wait" is the top stall).
 template <typename T, int N>
@@ -202,15 +224,19 @@ constexpr int pencil_min_ctas()
 // STREAM: the G rows of consecutive cells form one stream through the ring (rows are requested across
 // the cell boundary); otherwise the ring restarts with every cell (rows 0 .. RD-2 requested at the top of
 // the cell), which needs fewer registers.
-template <typename T, int P, int NQ, int CPB, int RD, bool UPF, bool STREAM>
+// PAIRED (fp32 only): the contractions run on FFMA2 with the tables of `ptab`.
+template <typename T, int P, int NQ, int CPB, int RD, bool UPF, bool STREAM, bool PAIRED>
 __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, pencil_min_ctas<T, P, NQ, CPB, RD>())
     stiffness_pencil_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ G,
                             const T* __restrict__ cell_constants,
                             const std::int32_t* __restrict__ mdofmap,
                             const std::int32_t* __restrict__ cells, int ncells,
-                            const __grid_constant__ SlabTables<T, P + 1, NQ> tab)
+                            const __grid_constant__ SlabTables<T, P + 1, NQ> tab,
+                            const __grid_constant__ PencilPairTables<PAIRED ? P + 1 : 1, PAIRED ? NQ : 1> ptab)
 {
+  static_assert(!PAIRED || sizeof(T) == 4, "FFMA2 is an fp32 instruction");
   using C = PencilConfig<T, P, NQ, CPB, RD>;
+  constexpr int NQP = (NQ + 1) / 2, NDP = (P + 2) / 2;
   constexpr int ND = C::ND, TPC = C::TPC, NQ3 = TPC * NQ, ND2 = ND * ND, ND3 = ND2 * ND;
   constexpr int S1I = C::S1I, S1J = C::S1J, S1V = C::S1V, S2I = C::S2I, S2V = C::S2V;
   constexpr int OUTER = sizeof(T) == 8 ? 1 : NQ; // unroll factor of the outer loop of each phase
@@ -338,11 +364,35 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
         }
         uv[k] *= kappa; // kappa folded into the input: y = A(kappa) u = A(1) (kappa u)
       }
-#pragma unroll OUTER
-      for (int qz = 0; qz < NQ; ++qz)
+      if constexpr (PAIRED)
       {
-        s1_own[qz] = pencil_dot<T, ND>(tab.phi + qz * ND, uv);
-        s1_own[S1V + qz] = pencil_dot<T, ND>(tab.dphi + qz * ND, uv);
+        float2 pz2[NQP], dz2[NQP];
+#pragma unroll
+        for (int qp = 0; qp < NQP; ++qp)
+          pz2[qp] = make_float2(0.f, 0.f), dz2[qp] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+#pragma unroll
+          for (int qp = 0; qp < NQP; ++qp)
+          {
+            pz2[qp] = pair_fma(uv[k], ptab.fphi[k * NQP + qp], pz2[qp]);
+            dz2[qp] = pair_fma(uv[k], ptab.fdphi[k * NQP + qp], dz2[qp]);
+          }
+#pragma unroll
+        for (int qz = 0; qz < NQ; ++qz)
+        {
+          s1_own[qz] = pair_get(pz2, qz);
+          s1_own[S1V + qz] = pair_get(dz2, qz);
+        }
+      }
+      else
+      {
+#pragma unroll OUTER
+        for (int qz = 0; qz < NQ; ++qz)
+        {
+          s1_own[qz] = pencil_dot<T, ND>(tab.phi + qz * ND, uv);
+          s1_own[S1V + qz] = pencil_dot<T, ND>(tab.dphi + qz * ND, uv);
+        }
       }
     }
     std::int32_t ndof[ND];
@@ -359,12 +409,38 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
         pzv[j] = s1_col[j * S1J];
         dzv[j] = s1_col[S1V + j * S1J];
       }
-#pragma unroll OUTER
-      for (int qy = 0; qy < NQ; ++qy)
+      if constexpr (PAIRED)
       {
-        s2_col[qy * NQ] = pencil_dot<T, ND>(tab.phi + qy * ND, pzv);
-        s2_col[S2V + qy * NQ] = pencil_dot<T, ND>(tab.dphi + qy * ND, pzv);
-        s2_col[2 * S2V + qy * NQ] = pencil_dot<T, ND>(tab.phi + qy * ND, dzv);
+        float2 a2[NQP], b2[NQP], c2[NQP];
+#pragma unroll
+        for (int qp = 0; qp < NQP; ++qp)
+          a2[qp] = make_float2(0.f, 0.f), b2[qp] = make_float2(0.f, 0.f), c2[qp] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < ND; ++j)
+#pragma unroll
+          for (int qp = 0; qp < NQP; ++qp)
+          {
+            a2[qp] = pair_fma(pzv[j], ptab.fphi[j * NQP + qp], a2[qp]);
+            b2[qp] = pair_fma(pzv[j], ptab.fdphi[j * NQP + qp], b2[qp]);
+            c2[qp] = pair_fma(dzv[j], ptab.fphi[j * NQP + qp], c2[qp]);
+          }
+#pragma unroll
+        for (int qy = 0; qy < NQ; ++qy)
+        {
+          s2_col[qy * NQ] = pair_get(a2, qy);
+          s2_col[S2V + qy * NQ] = pair_get(b2, qy);
+          s2_col[2 * S2V + qy * NQ] = pair_get(c2, qy);
+        }
+      }
+      else
+      {
+#pragma unroll OUTER
+        for (int qy = 0; qy < NQ; ++qy)
+        {
+          s2_col[qy * NQ] = pencil_dot<T, ND>(tab.phi + qy * ND, pzv);
+          s2_col[S2V + qy * NQ] = pencil_dot<T, ND>(tab.dphi + qy * ND, pzv);
+          s2_col[2 * S2V + qy * NQ] = pencil_dot<T, ND>(tab.phi + qy * ND, dzv);
+        }
       }
     }
     __syncthreads();
@@ -381,6 +457,27 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
         Cz[i] = s2_own[2 * S2V + i * S2I];
         oA[i] = 0, oB[i] = 0, oC[i] = 0;
       }
+      // PAIRED: the gradient at all nq points of the line first (needs no G), outputs as pairs
+      float2 gx2[PAIRED ? NQP : 1], gy2[PAIRED ? NQP : 1], gz2[PAIRED ? NQP : 1];
+      float2 oA2[PAIRED ? NDP : 1], oB2[PAIRED ? NDP : 1], oC2[PAIRED ? NDP : 1];
+      if constexpr (PAIRED)
+      {
+#pragma unroll
+        for (int qp = 0; qp < NQP; ++qp)
+          gx2[qp] = make_float2(0.f, 0.f), gy2[qp] = make_float2(0.f, 0.f), gz2[qp] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int ip = 0; ip < NDP; ++ip)
+          oA2[ip] = make_float2(0.f, 0.f), oB2[ip] = make_float2(0.f, 0.f), oC2[ip] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int i = 0; i < ND; ++i)
+#pragma unroll
+          for (int qp = 0; qp < NQP; ++qp)
+          {
+            gx2[qp] = pair_fma(A[i], ptab.fdphi[i * NQP + qp], gx2[qp]);
+            gy2[qp] = pair_fma(B[i], ptab.fphi[i * NQP + qp], gy2[qp]);
+            gz2[qp] = pair_fma(Cz[i], ptab.fphi[i * NQP + qp], gz2[qp]);
+          }
+      }
 #pragma unroll OUTER
       for (int qx = 0; qx < NQ; ++qx)
       {
@@ -391,9 +488,15 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
                 G5 = gr[5 * TPC];
         if constexpr (STREAM)
           ring_rd = (ring_rd == ring + (RD - 1) * SLOT) ? ring : ring_rd + SLOT;
-        const T gx = pencil_dot<T, ND>(tab.dphi + qx * ND, A);
-        const T gy = pencil_dot<T, ND>(tab.phi + qx * ND, B);
-        const T gz = pencil_dot<T, ND>(tab.phi + qx * ND, Cz);
+        T gx, gy, gz;
+        if constexpr (PAIRED)
+          gx = pair_get(gx2, qx), gy = pair_get(gy2, qx), gz = pair_get(gz2, qx);
+        else
+        {
+          gx = pencil_dot<T, ND>(tab.dphi + qx * ND, A);
+          gy = pencil_dot<T, ND>(tab.phi + qx * ND, B);
+          gz = pencil_dot<T, ND>(tab.phi + qx * ND, Cz);
+        }
         const T fx = G0 * gx + G1 * gy + G2 * gz;
         const T fy = G1 * gx + G3 * gy + G4 * gz;
         const T fz = G2 * gx + G4 * gy + G5 * gz;
@@ -412,21 +515,34 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
         else if (qx + RD - 1 < NQ)
           issue_row(ring_base + ((qx + RD - 1) % RD) * SLOT_BYTES, g_cur, qx + RD - 1);
         cp_async_commit(); // also when empty: keeps the group count uniform
-#pragma unroll
-        for (int i = 0; i < ND; ++i)
+        if constexpr (PAIRED)
         {
-          oA[i] += tab.dphi[qx * ND + i] * fx;
-          oB[i] += tab.phi[qx * ND + i] * fy;
-          oC[i] += tab.phi[qx * ND + i] * fz;
+#pragma unroll
+          for (int ip = 0; ip < NDP; ++ip)
+          {
+            oA2[ip] = pair_fma(fx, ptab.bdphi[qx * NDP + ip], oA2[ip]);
+            oB2[ip] = pair_fma(fy, ptab.bphi[qx * NDP + ip], oB2[ip]);
+            oC2[ip] = pair_fma(fz, ptab.bphi[qx * NDP + ip], oC2[ip]);
+          }
+        }
+        else
+        {
+#pragma unroll
+          for (int i = 0; i < ND; ++i)
+          {
+            oA[i] += tab.dphi[qx * ND + i] * fx;
+            oB[i] += tab.phi[qx * ND + i] * fy;
+            oC[i] += tab.phi[qx * ND + i] * fz;
+          }
         }
       }
       // the thread overwrites exactly the entries it read: no barrier between the read and the write
 #pragma unroll
       for (int i = 0; i < ND; ++i)
       {
-        s2_own[i * S2I] = oA[i];
-        s2_own[S2V + i * S2I] = oB[i];
-        s2_own[2 * S2V + i * S2I] = oC[i];
+        s2_own[i * S2I] = PAIRED ? T(pair_get(oA2, i)) : oA[i];
+        s2_own[S2V + i * S2I] = PAIRED ? T(pair_get(oB2, i)) : oB[i];
+        s2_own[2 * S2V + i * S2I] = PAIRED ? T(pair_get(oC2, i)) : oC[i];
       }
     }
     // next cell's input values: in flight during phases 4 and 5 (registers are free again)
@@ -443,26 +559,46 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
     if (act2)
     {
       T pz[ND], dz[ND];
+      float2 pz2[PAIRED ? NDP : 1], dz2[PAIRED ? NDP : 1];
 #pragma unroll
       for (int j = 0; j < ND; ++j)
         pz[j] = 0, dz[j] = 0;
+      if constexpr (PAIRED)
+      {
+#pragma unroll
+        for (int jp = 0; jp < NDP; ++jp)
+          pz2[jp] = make_float2(0.f, 0.f), dz2[jp] = make_float2(0.f, 0.f);
+      }
 #pragma unroll OUTER
       for (int qy = 0; qy < NQ; ++qy)
       {
         const T a = s2_col[qy * NQ], b = s2_col[S2V + qy * NQ], cz = s2_col[2 * S2V + qy * NQ];
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
+        if constexpr (PAIRED)
         {
-          pz[j] += tab.phi[qy * ND + j] * a;
-          pz[j] += tab.dphi[qy * ND + j] * b;
-          dz[j] += tab.phi[qy * ND + j] * cz;
+#pragma unroll
+          for (int jp = 0; jp < NDP; ++jp)
+          {
+            pz2[jp] = pair_fma(a, ptab.bphi[qy * NDP + jp], pz2[jp]);
+            pz2[jp] = pair_fma(b, ptab.bdphi[qy * NDP + jp], pz2[jp]);
+            dz2[jp] = pair_fma(cz, ptab.bphi[qy * NDP + jp], dz2[jp]);
+          }
+        }
+        else
+        {
+#pragma unroll
+          for (int j = 0; j < ND; ++j)
+          {
+            pz[j] += tab.phi[qy * ND + j] * a;
+            pz[j] += tab.dphi[qy * ND + j] * b;
+            dz[j] += tab.phi[qy * ND + j] * cz;
+          }
         }
       }
 #pragma unroll
       for (int j = 0; j < ND; ++j)
       {
-        s1_col[j * S1J] = pz[j];
-        s1_col[S1V + j * S1J] = dz[j];
+        s1_col[j * S1J] = PAIRED ? T(pair_get(pz2, j)) : pz[j];
+        s1_col[S1V + j * S1J] = PAIRED ? T(pair_get(dz2, j)) : dz[j];
       }
     }
     __syncthreads();
@@ -471,24 +607,43 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
     if (act1)
     {
       T out[ND];
+      float2 out2[PAIRED ? NDP : 1];
 #pragma unroll
       for (int k = 0; k < ND; ++k)
         out[k] = 0;
+      if constexpr (PAIRED)
+      {
+#pragma unroll
+        for (int kp = 0; kp < NDP; ++kp)
+          out2[kp] = make_float2(0.f, 0.f);
+      }
 #pragma unroll OUTER
       for (int qz = 0; qz < NQ; ++qz)
       {
         const T pz = s1_own[qz], dz = s1_own[S1V + qz];
-#pragma unroll
-        for (int k = 0; k < ND; ++k)
+        if constexpr (PAIRED)
         {
-          out[k] += tab.phi[qz * ND + k] * pz;
-          out[k] += tab.dphi[qz * ND + k] * dz;
+#pragma unroll
+          for (int kp = 0; kp < NDP; ++kp)
+          {
+            out2[kp] = pair_fma(pz, ptab.bphi[qz * NDP + kp], out2[kp]);
+            out2[kp] = pair_fma(dz, ptab.bdphi[qz * NDP + kp], out2[kp]);
+          }
+        }
+        else
+        {
+#pragma unroll
+          for (int k = 0; k < ND; ++k)
+          {
+            out[k] += tab.phi[qz * ND + k] * pz;
+            out[k] += tab.dphi[qz * ND + k] * dz;
+          }
         }
       }
 #pragma unroll
       for (int k = 0; k < ND; ++k)
         if (dof[k] >= 0)
-          red_add(y + dof[k], out[k]);
+          red_add(y + dof[k], PAIRED ? T(pair_get(out2, k)) : out[k]);
     }
     // Phases 1 and 5 touch the same S1 entries from the same thread, so the next cell's phase 1 may
     // start at once; its phase 2 writes S2 only after the barrier that follows phase 1, which every

@@ -1,6 +1,6 @@
-"""The pencil kernel (csrc/stiffness_pencil.cuh) against the oracle, for the three G-ring settings.
+"""The pencil kernel (csrc/stiffness_pencil.cuh) against the oracle, for the three G-ring settings and the FFMA2 variant.
 
-The setting is latched per process (BD_PENCIL_RING), so the cases run in a worker process."""
+The settings are latched per process (BD_PENCIL_RING, BD_PENCIL_PAIRED), so the cases run in a worker process."""
 import json
 import os
 import subprocess
@@ -14,9 +14,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 @pytest.mark.parametrize("degree", [5, 6, 7])
-@pytest.mark.parametrize("ring", ["0", "1", "2"])
-def test_pencil_kernel_matches_oracle(ring, degree):
-    env = dict(os.environ, BD_PENCIL_RING=ring, CUDA_LAUNCH_BLOCKING="1")
+@pytest.mark.parametrize("ring,paired", [("0", "0"), ("1", "0"), ("2", "0"), ("0", "1")])
+def test_pencil_kernel_matches_oracle(ring, paired, degree):
+    env = dict(os.environ, BD_PENCIL_RING=ring, BD_PENCIL_PAIRED=paired, CUDA_LAUNCH_BLOCKING="1")
     env.pop("BD_STIFFNESS_VARIANT", None)
     r = subprocess.run([sys.executable, os.path.join(HERE, "pencil_worker.py"), str(degree)], env=env,
                        capture_output=True, text=True, timeout=900)
