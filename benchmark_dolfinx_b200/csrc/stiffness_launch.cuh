@@ -12,7 +12,7 @@ namespace bd
 // it is instantiated (env BD_STIFFNESS_VARIANT = slab | tma | pencil)
 int stiffness_variant();
 int pencil_ring_variant();   // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead
-int pencil_paired_variant(); // env BD_PENCIL_PAIRED: 1 = FFMA2 contractions in fp32
+int pencil_paired_variant(); // env BD_PENCIL_PAIRED: 0 = default (FFMA2 contractions for fp32 nq = 9), 1 = on, 2 = off
 
 struct StiffnessArgs
 {
@@ -300,8 +300,10 @@ int launch_stiffness_pencil(const StiffnessArgs& a)
     const bool full = ring == 2 || (ring == 0 && sizeof(T) == 4);
     if constexpr (sizeof(T) == 4)
     {
-      // BD_PENCIL_PAIRED = 1: contractions on FFMA2 (experiment)
-      if (full && pencil_paired_variant() == 1)
+      // contractions on FFMA2: measured +16 % at nq = 9, nothing at nq = 7, 8 (profiles/r1_pencil_paired_ab.txt);
+      // BD_PENCIL_PAIRED = 1 / 2 forces it on / off
+      const int pv = pencil_paired_variant();
+      if (full && (pv == 1 || (pv == 0 && NQ == 9)))
         return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true, true>(a);
     }
     if (full)

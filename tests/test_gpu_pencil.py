@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 @pytest.mark.parametrize("degree", [5, 6, 7])
-@pytest.mark.parametrize("ring,paired", [("0", "0"), ("1", "0"), ("2", "0"), ("0", "1")])
+@pytest.mark.parametrize("ring,paired", [("0", "0"), ("1", "0"), ("2", "0"), ("0", "1"), ("0", "2")])
 def test_pencil_kernel_matches_oracle(ring, paired, degree):
     env = dict(os.environ, BD_PENCIL_RING=ring, BD_PENCIL_PAIRED=paired, CUDA_LAUNCH_BLOCKING="1")
     env.pop("BD_STIFFNESS_VARIANT", None)
