@@ -15,7 +15,7 @@ def _global_ids(bd, mesh, n, degree):
 
 
 @pytest.mark.parametrize("nranks", [2, 4, 8])
-@pytest.mark.parametrize("degree,qmode", [(2, 1), (3, 0)])
+@pytest.mark.parametrize("degree,qmode", [(2, 1), (3, 0), (6, 1), (7, 1)])  # slab, slab, DMMA, pencil kernels
 def test_partitioned_apply_equals_single_rank(nranks, degree, qmode):
     import torch
     import benchmark_dolfinx_b200 as bd
