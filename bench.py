@@ -286,6 +286,10 @@ def main():
     ap.add_argument("--no-cg", action="store_true", help="skip the CG leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
+    ap.add_argument("--reference-gpu-kernel", action="store_true",
+                    help="also time the reference's own CUDA kernel (oracle/_ref/libref_gpu.so, test "
+                         "infrastructure) on this GPU; off by default: the default run executes nothing "
+                         "under oracle/ except the CPU baseline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -458,7 +462,7 @@ def main():
     #      sm_100a, oracle/_ref/libref_gpu.so) with its own launch shape, on a smaller mesh of the same
     #      degree (its G layout needs a second copy of G), timed with CUDA events on the same GPU
     ref_gpu = None
-    if world == 1 and rank == 0 and not args.no_cpu:
+    if world == 1 and rank == 0 and args.reference_gpu_kernel:
         try:
             ref_gpu = reference_gpu_kernel_leg(bd, degree, qmode, dtype, min(args.ndofs, 100_000_000),
                                                max(3, min(args.steps, 10)))
