@@ -66,6 +66,15 @@ int pencil_ring_variant()
   return v;
 }
 
+int slab_f2_variant()
+{
+  static const int v = [] {
+    const char* e = std::getenv("BD_SLAB_F2");
+    return e ? std::atoi(e) : 0;
+  }();
+  return v;
+}
+
 int pencil_paired_variant()
 {
   static const int v = [] {

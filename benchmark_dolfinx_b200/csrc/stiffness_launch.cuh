@@ -5,6 +5,7 @@
 #include "stiffness.cuh"
 #include "stiffness_slab.cuh"
 #include "stiffness_pencil.cuh"
+#include "stiffness_slab_f2_kernel.cuh"
 
 namespace bd
 {
@@ -146,7 +147,46 @@ int launch_stiffness_slab_tma_cfg(const StiffnessArgs& a)
   }
 }
 
+// The fp32 slab kernel with FFMA2 phases (stiffness_slab_f2.cuh): qmode 1, nq <= 5, the default tuning.
+template <int P, int NQ>
+int launch_stiffness_slab_tma_f2(const StiffnessArgs& a)
+{
+  using TU = SlabTmaTuning<NQ>;
+  static_assert(NQ <= 5 && TU::Q0C == NQ && TU::WARPS == 1 && TU::PREFETCH, "FFMA2 slab kernel: nq <= 5 tuning");
+  using C = SlabConfig<float, P, NQ>;
+  using TC = SlabTmaConfig<float, P, NQ, TU::NSTAGE, NQ, 1>;
+  constexpr int ND = P + 1;
+  if (!a.mdofmap)
+    return fail(BD_ERR_INVALID_ARGUMENT, "the asynchronous-copy kernel needs the masked dofmap");
+  auto kernel = stiffness_slab_tma_f2_kernel<P, NQ, TU::NSTAGE, 1, true>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, TC::THREADS, TC::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  SlabTables<float, ND, NQ> tab;
+  fill_slab_tables<float, ND, NQ, false>(tab, a.phi0_host, a.dphi1_host);
+  SlabPairTables<ND, NQ> ptab;
+  fill_slab_pair_tables<ND, NQ>(ptab, tab.phi, tab.dphi);
+  const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(nbatches < max_grid ? nbatches : max_grid);
+  kernel<<<grid, TC::THREADS, TC::CTA_SMEM, a.stream>>>(
+      static_cast<const float*>(a.u), static_cast<float*>(a.y), static_cast<const float*>(a.G),
+      static_cast<const float*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), ptab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
 int slab_tune_variant(); // env BD_SLAB_TUNE (experiments), 0 = default
+int slab_f2_variant();   // env BD_SLAB_F2: 1 = FFMA2 phases for fp32, qmode 1, nq <= 5 (experiment)
 
 template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_slab_tma(const StiffnessArgs& a)
@@ -159,6 +199,11 @@ int launch_stiffness_slab_tma(const StiffnessArgs& a)
     // default   -> ring of 2 slots, 1 warp per CTA (7 warps/SM): measured 15.2 vs 16.1 ms at Q3/300M
     if (slab_tune_variant() == 1)
       return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, 3, NQ, 2, true>(a);
+  }
+  if constexpr (sizeof(T) == 4 && !IDENTITY && NQ <= 5)
+  {
+    if (slab_f2_variant() == 1)
+      return launch_stiffness_slab_tma_f2<P, NQ>(a);
   }
   // the gather prefetch needs 3 * nd^2 extra registers: affordable up to nd = 5
   constexpr bool PF = TU::PREFETCH || (NQ == 6 && P + 1 <= 5);

@@ -158,7 +158,7 @@ __device__ __forceinline__ void pencil_load_dofs(const std::int32_t* row, std::i
   }
 }
 
-// fp32 tables for the FFMA2 variant (two fp32 FMAs per instruction: a scalar from a register times a
+// fp32 tables for the FFMA2 variant (pair_fma, stiffness_slab_f2.cuh: a scalar from a register times a
 // pair of table entries from a uniform register, added to a register pair).  Forward phases pair two
 // neighbouring quadrature points, backward phases two neighbouring dofs; odd extents are zero padded.
 template <int ND, int NQ>
@@ -170,16 +170,6 @@ struct PencilPairTables
   float2 bphi[NQ * NDP];  // [q][kp] = (Phi[q][2kp],  Phi[q][2kp+1])
   float2 bdphi[NQ * NDP]; // [q][kp] = (DPhi[q][2kp], DPhi[q][2kp+1])
 };
-__device__ __forceinline__ float2 pair_fma(float s, float2 t, float2 acc)
-{
-  return __ffma2_rn(make_float2(s, s), t, acc); // SASS: FFMA2 R, R.F32, UR.F32x2, R.F32x2
-}
-template <int N>
-__device__ __forceinline__ float pair_get(const float2 (&v)[N], int i)
-{
-  return (i & 1) ? v[i >> 1].y : v[i >> 1].x;
-}
-
 // sum_k row[k] * v[k].  fp64: two partial sums -- the rolled loops leave only a few independent DFMA
 // chains per warp, and with 9-12 warps per SM their latency shows (ncu: "wait" is the top stall).
 template <typename T, int N>

@@ -30,6 +30,8 @@
 
 #include <cstdint>
 
+#include "stiffness_slab_f2.cuh"
+
 namespace bd
 {
 template <typename T, int ND, int NQ>
@@ -111,7 +113,7 @@ inline std::int64_t slab_g_size(int nq, std::int64_t ncells)
 
 // Forward X phase of lane (c, i): y/z contractions of the dof plane `ul` -> a_x, a_y, a_z in the cube.
 template <typename T, int ND, int NQ, int RL, int CUBE, bool IDENTITY>
-__device__ __forceinline__ void slab_forward_x(const SlabTables<T, ND, NQ>& tab, const T (&ul)[ND * ND],
+BD_PHASE_FN void slab_forward_x(const SlabTables<T, ND, NQ>& tab, const T (&ul)[ND * ND],
                                                T* __restrict__ dst0)
 {
   // dst0 = cube + i*RL + rbase ; element (q1, q2) at dst0[q1*ND*RL + q2]
@@ -286,7 +288,7 @@ __device__ __forceinline__ void slab_backward_x_rolled(const SlabTables<T, ND, N
 // Q0B is an ordinary argument, but every call site sits in a fully unrolled loop, so after inlining
 // all table indices are compile-time constants.
 template <typename T, int ND, int NQ, int ROW, bool IDENTITY, int Q0N, bool STREAM_LDG, bool SCALE = true>
-__device__ __forceinline__ void slab_z_points(const SlabTables<T, ND, NQ>& tab, const T (&ax)[ND],
+BD_PHASE_FN void slab_z_points(const SlabTables<T, ND, NQ>& tab, const T (&ax)[ND],
                                               const T (&ay)[ND], const T (&az)[ND], T (&bx)[ND],
                                               T (&by)[ND], T (&bz)[ND], const T* __restrict__ g, T kappa,
                                               const int Q0B)
@@ -373,7 +375,7 @@ __device__ __forceinline__ void slab_z_points(const SlabTables<T, ND, NQ>& tab, 
 
 // Backward X phase of lane (c, i): transposed y/z contractions of b_x, b_y, b_z -> out (dof plane i).
 template <typename T, int ND, int NQ, int RL, int CUBE, bool IDENTITY>
-__device__ __forceinline__ void slab_backward_x(const SlabTables<T, ND, NQ>& tab, const T* __restrict__ src0,
+BD_PHASE_FN void slab_backward_x(const SlabTables<T, ND, NQ>& tab, const T* __restrict__ src0,
                                                 T (&out)[ND * ND])
 {
 #pragma unroll
