@@ -75,6 +75,15 @@ int slab_f2_variant()
   return v;
 }
 
+int pencil_bulk_variant()
+{
+  static const int v = [] {
+    const char* e = std::getenv("BD_PENCIL_BULK");
+    return e ? std::atoi(e) : 0;
+  }();
+  return v;
+}
+
 int pencil_paired_variant()
 {
   static const int v = [] {

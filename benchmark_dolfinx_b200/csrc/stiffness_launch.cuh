@@ -6,6 +6,7 @@
 #include "stiffness_slab.cuh"
 #include "stiffness_pencil.cuh"
 #include "stiffness_slab_f2_kernel.cuh"
+#include "stiffness_pencil_bulk.cuh"
 
 namespace bd
 {
@@ -13,6 +14,7 @@ namespace bd
 // it is instantiated (env BD_STIFFNESS_VARIANT = slab | tma | pencil)
 int stiffness_variant();
 int pencil_ring_variant();   // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead
+int pencil_bulk_variant();   // env BD_PENCIL_BULK: 1 = stiffness_pencil_bulk_kernel where it applies (fp32, nq = 8)
 int pencil_paired_variant(); // env BD_PENCIL_PAIRED: 0 = default (FFMA2 contractions for fp32 nq = 9), 1 = on, 2 = off
 
 struct StiffnessArgs
@@ -322,6 +324,54 @@ int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
+// The experimental fp32 pencil kernel with one bulk copy of G per cell (stiffness_pencil_bulk.cuh).
+template <int P, int NQ, bool PAIRED>
+int launch_stiffness_pencil_bulk(const StiffnessArgs& a)
+{
+  using C = PencilBulkConfig<P, NQ>;
+  constexpr int ND = P + 1;
+  auto kernel = stiffness_pencil_bulk_kernel<P, NQ, PAIRED>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, C::THREADS, C::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  SlabTables<float, ND, NQ> tab;
+  fill_slab_tables<float, ND, NQ, false>(tab, a.phi0_host, a.dphi1_host);
+  PencilPairTables<PAIRED ? ND : 1, PAIRED ? NQ : 1> ptab{};
+  if constexpr (PAIRED)
+  {
+    constexpr int NQP = (NQ + 1) / 2, NDP = (ND + 1) / 2;
+    auto at = [](const float* t, int q, int k) { return (q < NQ && k < ND) ? t[q * ND + k] : 0.f; };
+    for (int k = 0; k < ND; ++k)
+      for (int qp = 0; qp < NQP; ++qp)
+      {
+        ptab.fphi[k * NQP + qp] = make_float2(at(tab.phi, 2 * qp, k), at(tab.phi, 2 * qp + 1, k));
+        ptab.fdphi[k * NQP + qp] = make_float2(at(tab.dphi, 2 * qp, k), at(tab.dphi, 2 * qp + 1, k));
+      }
+    for (int q = 0; q < NQ; ++q)
+      for (int kp = 0; kp < NDP; ++kp)
+      {
+        ptab.bphi[q * NDP + kp] = make_float2(at(tab.phi, q, 2 * kp), at(tab.phi, q, 2 * kp + 1));
+        ptab.bdphi[q * NDP + kp] = make_float2(at(tab.dphi, q, 2 * kp), at(tab.dphi, q, 2 * kp + 1));
+      }
+  }
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(a.ncells < max_grid ? a.ncells : max_grid);
+  kernel<<<grid, C::THREADS, C::CTA_SMEM, a.stream>>>(
+      static_cast<const float*>(a.u), static_cast<float*>(a.y), static_cast<const float*>(a.G),
+      static_cast<const float*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab, ptab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
 // `a.G` in the reference layout (g_layout 0), `a.mdofmap` required.
 template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_pencil(const StiffnessArgs& a)
@@ -340,6 +390,13 @@ int launch_stiffness_pencil(const StiffnessArgs& a)
     // ahead and the next cell's input prefetched; fp64: ring of 3 rows and no input prefetch, which keeps
     // the kernel at <= 160 registers and 40 KB, i.e. 4 CTAs (12 warps) per SM.  BD_PENCIL_RING = 1 / 2
     // forces the short / the full ring (experiments).
+    if constexpr (sizeof(T) == 4 && PencilBulkConfig<P, NQ>::SUPPORTED)
+    {
+      // BD_PENCIL_BULK = 1: one bulk copy of G per cell + cell index / kappa a cell ahead (experiment)
+      if (pencil_bulk_variant() == 1)
+        return pencil_paired_variant() == 1 ? launch_stiffness_pencil_bulk<P, NQ, true>(a)
+                                            : launch_stiffness_pencil_bulk<P, NQ, false>(a);
+    }
     constexpr int FULL = NQ + 1;
     const int ring = pencil_ring_variant();
     const bool full = ring == 2 || (ring == 0 && sizeof(T) == 4);
