@@ -6,7 +6,7 @@
 
 namespace bd
 {
-template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, bool PREFETCH>
+template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, int PREFETCH>
 static int launch_mma8(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
@@ -58,11 +58,15 @@ static int env_int(const char* name, int dflt)
 template <typename TS, int P, int NQ, bool IDENTITY>
 static int launch_mma8_tuned(const StiffnessArgs& a)
 {
-  // tuning knobs for experiments: BD_MMA8_WARPS (2|4 warps per CTA), BD_MMA8_PREFETCH (0|1)
+  // tuning knobs for experiments: BD_MMA8_WARPS (2|4 warps per CTA), BD_MMA8_PREFETCH (0|1|2, see the kernel)
   static const int warps = env_int("BD_MMA8_WARPS", 4), prefetch = env_int("BD_MMA8_PREFETCH", 1);
   if (warps == 4)
-    return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 4, true>(a) : launch_mma8<TS, P, NQ, IDENTITY, 4, false>(a);
-  return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 2, true>(a) : launch_mma8<TS, P, NQ, IDENTITY, 2, false>(a);
+  {
+    if (prefetch == 2)
+      return launch_mma8<TS, P, NQ, IDENTITY, 4, 2>(a);
+    return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 4, 1>(a) : launch_mma8<TS, P, NQ, IDENTITY, 4, 0>(a);
+  }
+  return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 2, 1>(a) : launch_mma8<TS, P, NQ, IDENTITY, 2, 0>(a);
 }
 
 int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const StiffnessArgs& a)
