@@ -13,7 +13,7 @@ namespace bd
 // 0 = default choice, 1 = plain slab kernel, 2 = asynchronous-copy slab kernel, 3 = pencil kernel wherever
 // it is instantiated (env BD_STIFFNESS_VARIANT = slab | tma | pencil)
 int stiffness_variant();
-int pencil_ring_variant();   // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead
+int pencil_ring_variant();   // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead, 3 = 5 rows (fp64)
 int pencil_bulk_variant();   // env BD_PENCIL_BULK: 1 = stiffness_pencil_bulk_kernel where it applies (fp32, nq = 8)
 int pencil_paired_variant(); // env BD_PENCIL_PAIRED: 0 = default (FFMA2 contractions for fp32 nq = 9), 1 = on, 2 = off
 
@@ -410,6 +410,13 @@ int launch_stiffness_pencil(const StiffnessArgs& a)
     }
     if (full)
       return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true, false>(a);
+    if constexpr (sizeof(T) == 8)
+    {
+      // BD_PENCIL_RING = 3: ring of 5 rows restarted per cell (48 KB, still 4 CTAs/SM) -- experiment: ncu puts
+      // 17 % of the fp64 kernel's stall samples on the wait for a G row requested only 2 rows earlier
+      if (ring == 3)
+        return launch_stiffness_pencil_cfg<T, P, NQ, 1, 5, false, false, false>(a);
+    }
     return launch_stiffness_pencil_cfg<T, P, NQ, 1, 3, false, false, false>(a);
   }
 }

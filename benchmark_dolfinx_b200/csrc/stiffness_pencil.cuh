@@ -332,6 +332,7 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
           cp_async_commit();
         }
       }
+      ring_wr = ring_base + (RD - 1) * SLOT_BYTES; // row RD-1 goes into slot RD-1 (used when RD != 3)
     }
 
     // ---- phase 1: gather, BC masking (reference :153-170), z contraction
@@ -502,8 +503,22 @@ __global__ void __launch_bounds__(PencilConfig<T, P, NQ, CPB, RD>::THREADS, penc
             issue_row(ring_wr, g_next, qx + RD - 1 - NQ);
           ring_wr = (ring_wr == ring_base + (RD - 1) * SLOT_BYTES) ? ring_base : ring_wr + SLOT_BYTES;
         }
-        else if (qx + RD - 1 < NQ)
-          issue_row(ring_base + ((qx + RD - 1) % RD) * SLOT_BYTES, g_cur, qx + RD - 1);
+        else if constexpr (RD == 3)
+        {
+          // the shipped fp64 configuration: slot from the loop counter (its SASS is checked, see above)
+          if (qx + RD - 1 < NQ)
+            issue_row(ring_base + ((qx + RD - 1) % RD) * SLOT_BYTES, g_cur, qx + RD - 1);
+        }
+        else
+        {
+          // other depths: running destination address in an ordinary register (for RD = 5 ptxas emits the
+          // faulting LDGSTS form when the slot is derived from the loop counter)
+          if constexpr (OUTER == 1)
+            asm volatile("" : "+r"(ring_wr));
+          if (qx + RD - 1 < NQ)
+            issue_row(ring_wr, g_cur, qx + RD - 1);
+          ring_wr = (ring_wr == ring_base + (RD - 1) * SLOT_BYTES) ? ring_base : ring_wr + SLOT_BYTES;
+        }
         cp_async_commit(); // also when empty: keeps the group count uniform
         if constexpr (PAIRED)
         {

@@ -31,3 +31,9 @@ def test_dmma_kernel_with_value_prefetch():
                  ["6:1:f64:4000", "6:1:f64:400000", "7:0:f64:300000", "5:1:f64:300000", "6:0:f64:300000",
                   "7:0:f32:300000", "6:0:f32:300000"])
     assert all("mma8" in l["kernel"] for l in lines)
+
+
+def test_fp64_pencil_kernel_with_five_row_ring():
+    """BD_PENCIL_RING=3 (csrc/stiffness_pencil.cuh): ring of 5 G rows restarted per cell, fp64, nq = 9."""
+    lines = _run({"BD_PENCIL_RING": "3"}, ["7:1:f64:4000", "7:1:f64:450000"])
+    assert all("pencil" in l["kernel"] for l in lines)
