@@ -91,6 +91,11 @@ def device_information() -> str:
     return buf.value.decode()
 
 
+def debug_set_max_grid(max_ctas: int) -> None:
+    """Test hook: cap the grid of the persistent stiffness kernels (0 = no cap)."""
+    check(lib.bd_debug_set_max_grid(int(max_ctas)))
+
+
 def compute_mesh_size(ndofs_global: int, degree: int):
     """src/mesh.cpp:117-152."""
     out = (C.c_int64 * 3)()
@@ -472,6 +477,8 @@ def cg_solve(A: MatFreeLaplacianGPU, x, b, max_iter: int, rtol: float = 0.0, com
     (the CSR check operator) runs the same recurrence through the vector functions."""
     A._check_vec(x)
     A._check_vec(b)
+    if comm is None and getattr(A, "halo", None) is not None:
+        comm = A.halo.comm            # the sums must run over the ranks the halo plan spans
     if not isinstance(A, MatFreeLaplacianGPU):
         return _cg_solve_generic(A, x, b, max_iter, rtol, comm)
     its = C.c_int(0)

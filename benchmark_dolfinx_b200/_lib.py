@@ -69,6 +69,7 @@ class BoxMeshInfo(C.Structure):
 _V = C.c_void_p
 PROTOTYPES = {
     "bd_last_error": (C.c_char_p, []),
+    "bd_debug_set_max_grid": (C.c_int, [C.c_int]),
     "bd_device_information": (C.c_int, [C.c_char_p, C.c_size_t]),
     "bd_laplacian_create": (C.c_int, [C.POINTER(LaplacianDesc), C.POINTER(_V)]),
     "bd_laplacian_destroy": (C.c_int, [_V]),

@@ -147,6 +147,13 @@ extern "C" int bd_cg_solve(bd_laplacian* op, bd_halo* halo, bd_comm* comm, void*
   BD_REQUIRE(!halo || (halo->n_owned + halo->n_ghost == op->ndofs && halo->scalar_bits == op->scalar_bits),
              "halo plan does not match the operator");
   BD_REQUIRE(!(comm && comm->nranks > 1) || halo, "a multi-rank solve needs a halo plan");
+  // A multi-rank halo plan without a communicator would make every rank use its local dot products
+  // (ranks then diverge, and with rtol > 0 leave the loop at different iterations): the plan's own
+  // communicator is the one the sums must run over.
+  if (!comm && halo && halo->comm && halo->comm->nranks > 1)
+    comm = halo->comm;
+  BD_REQUIRE(!(comm && halo && halo->comm) || comm->nranks == halo->comm->nranks,
+             "bd_cg_solve: communicator and halo plan have different rank counts");
   return op->scalar_bits == 64
              ? cg_impl<double>(op, halo, comm, static_cast<double*>(x_dev),
                                static_cast<const double*>(b_dev), max_iter, rtol, iterations,

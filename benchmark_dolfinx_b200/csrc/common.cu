@@ -1,9 +1,13 @@
 #include "common.cuh"
 
+#include <atomic>
 #include <cstring>
 
 namespace bd
 {
+static std::atomic<int> g_debug_max_grid{0};
+int debug_max_grid() { return g_debug_max_grid.load(std::memory_order_relaxed); }
+
 std::string& last_error_slot()
 {
   static thread_local std::string slot;
@@ -37,6 +41,13 @@ int sm_count()
   return cached[dev];
 }
 } // namespace bd
+
+extern "C" int bd_debug_set_max_grid(int max_ctas)
+{
+  BD_REQUIRE(max_ctas >= 0, "bd_debug_set_max_grid: negative grid cap");
+  bd::g_debug_max_grid.store(max_ctas, std::memory_order_relaxed);
+  return BD_SUCCESS;
+}
 
 extern "C" const char* bd_last_error(void) { return bd::last_error_slot().c_str(); }
 

@@ -48,6 +48,19 @@ int sm_count();
 // B200: 148 SMs.  Grids of the streaming kernels are sized as a multiple of this.
 constexpr int kB200SMs = 148;
 
+// Test hook (bd_debug_set_max_grid): upper bound on the grid of every persistent stiffness kernel, 0 = none.
+// With a grid of 2-3 CTAs even a few-thousand-cell test mesh drives every warp through many batches, i.e.
+// through the steady state of the rings / prefetch rotations that the benchmark sizes spend all their time in.
+int debug_max_grid();
+inline std::int64_t clamp_grid(std::int64_t want, std::int64_t resident)
+{
+  std::int64_t g = want < resident ? want : resident;
+  const int cap = debug_max_grid();
+  if (cap > 0 && g > cap)
+    g = cap;
+  return g < 1 ? 1 : g;
+}
+
 template <typename T>
 struct scalar_traits;
 template <>

@@ -66,7 +66,7 @@ int launch_stiffness(const StiffnessArgs& a)
     tab.dphi[i] = dphi[i];
   const std::int64_t nbatches = (a.ncells + CPB - 1) / CPB;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-  const int grid = static_cast<int>(nbatches < max_grid ? nbatches : max_grid);
+  const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
   kernel<<<grid, THREADS, 0, a.stream>>>(
       static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
       static_cast<const T*>(a.cell_constants), a.dofmap, a.cells, static_cast<int>(a.ncells), a.bc,
@@ -140,7 +140,7 @@ int launch_stiffness_slab_tma_cfg(const StiffnessArgs& a)
     const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
     const std::int64_t want = (nbatches + TC::WARPS - 1) / TC::WARPS;
     const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-    const int grid = static_cast<int>(want < max_grid ? want : max_grid);
+    const int grid = static_cast<int>(clamp_grid(want, max_grid));
     kernel<<<grid, TC::THREADS, TC::CTA_SMEM, a.stream>>>(
         static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
         static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
@@ -179,7 +179,7 @@ int launch_stiffness_slab_tma_f2(const StiffnessArgs& a)
   fill_slab_pair_tables<ND, NQ>(ptab, tab.phi, tab.dphi);
   const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-  const int grid = static_cast<int>(nbatches < max_grid ? nbatches : max_grid);
+  const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
   kernel<<<grid, TC::THREADS, TC::CTA_SMEM, a.stream>>>(
       static_cast<const float*>(a.u), static_cast<float*>(a.y), static_cast<const float*>(a.G),
       static_cast<const float*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), ptab);
@@ -257,7 +257,7 @@ int launch_stiffness_slab(const StiffnessArgs& a)
   const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
   const std::int64_t want = (nbatches + C::WARPS - 1) / C::WARPS;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-  const int grid = static_cast<int>(want < max_grid ? want : max_grid);
+  const int grid = static_cast<int>(clamp_grid(want, max_grid));
   kernel<<<grid, C::THREADS, C::CTA_SMEM, a.stream>>>(
       static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.G),
       static_cast<const T*>(a.cell_constants), a.dofmap, a.cells, static_cast<int>(a.ncells), a.bc,
@@ -298,7 +298,7 @@ int launch_stiffness_pencil_cfg(const StiffnessArgs& a)
   fill_slab_tables<T, ND, NQ, false>(tab, a.phi0_host, a.dphi1_host);
   const std::int64_t nbatches = (a.ncells + CPB - 1) / CPB;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-  const int grid = static_cast<int>(nbatches < max_grid ? nbatches : max_grid);
+  const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
   PencilPairTables<PAIRED ? ND : 1, PAIRED ? NQ : 1> ptab{};
   if constexpr (PAIRED)
   {
@@ -364,7 +364,7 @@ int launch_stiffness_pencil_bulk(const StiffnessArgs& a)
       }
   }
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-  const int grid = static_cast<int>(a.ncells < max_grid ? a.ncells : max_grid);
+  const int grid = static_cast<int>(clamp_grid(a.ncells, max_grid));
   kernel<<<grid, C::THREADS, C::CTA_SMEM, a.stream>>>(
       static_cast<const float*>(a.u), static_cast<float*>(a.y), static_cast<const float*>(a.G),
       static_cast<const float*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab, ptab);

@@ -41,7 +41,7 @@ static int launch_mma8(const StiffnessArgs& a)
     }
   const std::int64_t want = (a.ncells + kMma8Warps - 1) / kMma8Warps;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-  const int grid = static_cast<int>(want < max_grid ? want : max_grid);
+  const int grid = static_cast<int>(clamp_grid(want, max_grid));
   kernel<<<grid, kMma8Warps * 32, smem, a.stream>>>(
       static_cast<const TS*>(a.u), static_cast<TS*>(a.y), static_cast<const TS*>(a.G),
       static_cast<const TS*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);

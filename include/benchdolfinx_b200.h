@@ -37,6 +37,13 @@ extern "C" {
 /* Message of the last error on this thread ("" if none). Never NULL. */
 const char* bd_last_error(void);
 
+/* Test hook, no counterpart in the reference (its kernels launch one CTA per cell,
+ * src/laplacian.hpp:298-306, so they have no persistent steady state to exercise): caps the
+ * grid of every persistent stiffness kernel at `max_ctas` CTAs (0 = no cap, the default).
+ * With 2-3 CTAs a test mesh of a few thousand cells drives each warp through many batches,
+ * which is where the benchmark sizes spend all their time.  Process-wide; not for production. */
+int bd_debug_set_max_grid(int max_ctas);
+
 /* Library / device banner (replaces get_device_information, src/util.cpp:10-52).
  * Writes at most `n` bytes including the terminator. */
 int bd_device_information(char* buf, size_t n);
@@ -168,7 +175,11 @@ int bd_dot(int scalar_bits, int64_t n, const void* a, const void* b, double* res
  *   - Vectors of up to BD_DOT_STATIC_MAX_N entries; longer ones are rejected with
  *     BD_ERR_INVALID_ARGUMENT (use bd_dot).
  *   - The first call on each device looks up the array's device address (that device must be
- *     current); make that first call before starting any stream capture.
+ *     current); make that first call before starting any stream capture.  CUDA loads device
+ *     code lazily: if no vector kernel of this library (bd_axpy, bd_dot, bd_set_value, ...) has
+ *     run on the device yet, that first call is also the one that loads the code and places the
+ *     array, so it has to happen while the device still has a little free memory -- i.e. before
+ *     the application hands the rest of it to its own pools.  Later calls take nothing.
  *   - All calls on a device share the array: two calls whose kernels can overlap on the GPU
  *     (different streams, or different host threads) race on it and give wrong sums; calls on
  *     one stream are safe.  The array keeps the previous call's partial sums; none of it needs

@@ -36,7 +36,17 @@ def test_static_dot_matches_bd_dot_twice_in_a_row(dtype):
         b = rng.uniform(-1, 1, n).astype(dtype)
         host.append(float(np.dot(a.astype(np.float64), b.astype(np.float64))))
         ad, bd_ = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+        if k == 1:
+            # The first call on a device may still load the library's device image (CUDA loads modules
+            # lazily), which is where the fixed array lives.  From the second call on nothing may be
+            # taken from the device: free memory as the driver reports it must not move.
+            torch.cuda.synchronize()
+            free_before, _ = torch.cuda.mem_get_info()
         check(lib.bd_dot_static(bits, n, ad.data_ptr(), bd_.data_ptr(), res.data_ptr() + 16 * k, stream))
+        if k == 1:
+            torch.cuda.synchronize()
+            free_after, _ = torch.cuda.mem_get_info()
+            assert free_after == free_before, "bd_dot_static changed the device's free memory"
         check(lib.bd_dot(bits, n, ad.data_ptr(), bd_.data_ptr(), res.data_ptr() + 16 * k + 8,
                          scratch.data_ptr(), stream))
         torch.cuda.synchronize()
