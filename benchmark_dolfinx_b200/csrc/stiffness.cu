@@ -48,51 +48,6 @@ int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::i
   return BD_SUCCESS;
 }
 
-int slab_tune_variant()
-{
-  static const int v = [] {
-    const char* e = std::getenv("BD_SLAB_TUNE");
-    return e ? std::atoi(e) : 0;
-  }();
-  return v;
-}
-
-int pencil_ring_variant()
-{
-  static const int v = [] {
-    const char* e = std::getenv("BD_PENCIL_RING");
-    return e ? std::atoi(e) : 0;
-  }();
-  return v;
-}
-
-int slab_f2_variant()
-{
-  static const int v = [] {
-    const char* e = std::getenv("BD_SLAB_F2");
-    return e ? std::atoi(e) : 0;
-  }();
-  return v;
-}
-
-int pencil_bulk_variant()
-{
-  static const int v = [] {
-    const char* e = std::getenv("BD_PENCIL_BULK");
-    return e ? std::atoi(e) : 0;
-  }();
-  return v;
-}
-
-int pencil_paired_variant()
-{
-  static const int v = [] {
-    const char* e = std::getenv("BD_PENCIL_PAIRED");
-    return e ? std::atoi(e) : 0;
-  }();
-  return v;
-}
-
 int preferred_g_layout(int scalar_bits, int degree, int nq)
 {
   // pencil kernel (reference layout): see pencil_instantiated() in stiffness_launch.cuh

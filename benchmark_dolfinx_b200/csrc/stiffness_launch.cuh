@@ -5,7 +5,6 @@
 #include "stiffness.cuh"
 #include "stiffness_slab.cuh"
 #include "stiffness_pencil.cuh"
-#include "stiffness_slab_f2_kernel.cuh"
 #include "stiffness_pencil_bulk.cuh"
 
 namespace bd
@@ -13,9 +12,6 @@ namespace bd
 // 0 = default choice, 1 = plain slab kernel, 2 = asynchronous-copy slab kernel, 3 = pencil kernel wherever
 // it is instantiated (env BD_STIFFNESS_VARIANT = slab | tma | pencil)
 int stiffness_variant();
-int pencil_ring_variant();   // env BD_PENCIL_RING: 0 = default, 1 = ring of 3 rows, 2 = a whole cell ahead, 3 = 5 rows (fp64)
-int pencil_bulk_variant();   // env BD_PENCIL_BULK: 1 = stiffness_pencil_bulk_kernel where it applies (fp32, nq = 8)
-int pencil_paired_variant(); // env BD_PENCIL_PAIRED: 0 = default (FFMA2 contractions for fp32 nq = 9), 1 = on, 2 = off
 
 struct StiffnessArgs
 {
@@ -149,64 +145,13 @@ int launch_stiffness_slab_tma_cfg(const StiffnessArgs& a)
   }
 }
 
-// The fp32 slab kernel with FFMA2 phases (stiffness_slab_f2.cuh): qmode 1, nq <= 5, the default tuning.
-template <int P, int NQ>
-int launch_stiffness_slab_tma_f2(const StiffnessArgs& a)
-{
-  using TU = SlabTmaTuning<NQ>;
-  static_assert(NQ <= 5 && TU::Q0C == NQ && TU::WARPS == 1 && TU::PREFETCH, "FFMA2 slab kernel: nq <= 5 tuning");
-  using C = SlabConfig<float, P, NQ>;
-  using TC = SlabTmaConfig<float, P, NQ, TU::NSTAGE, NQ, 1>;
-  constexpr int ND = P + 1;
-  if (!a.mdofmap)
-    return fail(BD_ERR_INVALID_ARGUMENT, "the asynchronous-copy kernel needs the masked dofmap");
-  auto kernel = stiffness_slab_tma_f2_kernel<P, NQ, TU::NSTAGE, 1, true>;
-  static thread_local int blocks_per_sm[64] = {0};
-  int dev = 0;
-  BD_CUDA_CHECK(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 64)
-    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
-  if (blocks_per_sm[dev] == 0)
-  {
-    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC::CTA_SMEM));
-    int nb = 0;
-    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, TC::THREADS, TC::CTA_SMEM));
-    blocks_per_sm[dev] = nb > 0 ? nb : 1;
-  }
-  SlabTables<float, ND, NQ> tab;
-  fill_slab_tables<float, ND, NQ, false>(tab, a.phi0_host, a.dphi1_host);
-  SlabPairTables<ND, NQ> ptab;
-  fill_slab_pair_tables<ND, NQ>(ptab, tab.phi, tab.dphi);
-  const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
-  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
-  const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
-  kernel<<<grid, TC::THREADS, TC::CTA_SMEM, a.stream>>>(
-      static_cast<const float*>(a.u), static_cast<float*>(a.y), static_cast<const float*>(a.G),
-      static_cast<const float*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), ptab);
-  BD_CUDA_CHECK(cudaGetLastError());
-  return BD_SUCCESS;
-}
-
-int slab_tune_variant(); // env BD_SLAB_TUNE (experiments), 0 = default
-int slab_f2_variant();   // env BD_SLAB_F2: 1 = FFMA2 phases for fp32, qmode 1, nq <= 5 (experiment)
-
 template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_slab_tma(const StiffnessArgs& a)
 {
   using TU = SlabTmaTuning<NQ>;
   constexpr int NSTAGE = (NQ == 7) ? 2 : TU::NSTAGE;
-  if constexpr (NQ <= 5)
-  {
-    // experiments: BD_SLAB_TUNE=1 -> ring of 3 slots, 2 warps per CTA (6 warps/SM at Q3 fp64);
-    // default   -> ring of 2 slots, 1 warp per CTA (7 warps/SM): measured 15.2 vs 16.1 ms at Q3/300M
-    if (slab_tune_variant() == 1)
-      return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, 3, NQ, 2, true>(a);
-  }
-  if constexpr (sizeof(T) == 4 && !IDENTITY && NQ <= 5)
-  {
-    if (slab_f2_variant() == 1)
-      return launch_stiffness_slab_tma_f2<P, NQ>(a);
-  }
+  // nq <= 5: ring of 2 slots, 1 warp per CTA (7 warps/SM at Q3 fp64) measured ahead of 3 slots / 2 warps per
+  // CTA (15.2 vs 16.1 ms at Q3/300M, round 1)
   // the gather prefetch needs 3 * nd^2 extra registers: affordable up to nd = 5
   constexpr bool PF = TU::PREFETCH || (NQ == 6 && P + 1 <= 5);
   return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, NSTAGE, TU::Q0C, TU::WARPS, PF>(a);
@@ -386,38 +331,19 @@ int launch_stiffness_pencil(const StiffnessArgs& a)
       return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
     if (!a.mdofmap)
       return fail(BD_ERR_INVALID_ARGUMENT, "the pencil kernel needs the masked dofmap");
-    // One cell per CTA throughout (measured best for nq = 7, 8, 9).  fp32: G requested a whole cell
-    // ahead and the next cell's input prefetched; fp64: ring of 3 rows and no input prefetch, which keeps
-    // the kernel at <= 160 registers and 40 KB, i.e. 4 CTAs (12 warps) per SM.  BD_PENCIL_RING = 1 / 2
-    // forces the short / the full ring (experiments).
+    // One cell per CTA throughout (measured best for nq = 7, 8, 9).  Choices measured on one B200
+    // (profiles/r1_pencil_*, profiles/r2_experiments_ab.txt):
+    //   fp32, nq = 8: one bulk copy of the cell's G block per cell (stiffness_pencil_bulk.cuh), 43.3 -> 52.0 GDoF/s;
+    //   fp32, nq = 7, 9: G rows requested a whole cell ahead, next cell's input prefetched; FFMA2 contractions at
+    //                    nq = 9 (+16 %), scalar at nq = 7;
+    //   fp64 (nq = 9): ring of 5 rows restarted per cell, no input prefetch (151 registers, 48 KB, 4 CTAs/SM),
+    //                  19.5 -> 21.2 GDoF/s against the 3-row ring.
     if constexpr (sizeof(T) == 4 && PencilBulkConfig<P, NQ>::SUPPORTED)
-    {
-      // BD_PENCIL_BULK = 1: one bulk copy of G per cell + cell index / kappa a cell ahead (experiment)
-      if (pencil_bulk_variant() == 1)
-        return pencil_paired_variant() == 1 ? launch_stiffness_pencil_bulk<P, NQ, true>(a)
-                                            : launch_stiffness_pencil_bulk<P, NQ, false>(a);
-    }
-    constexpr int FULL = NQ + 1;
-    const int ring = pencil_ring_variant();
-    const bool full = ring == 2 || (ring == 0 && sizeof(T) == 4);
-    if constexpr (sizeof(T) == 4)
-    {
-      // contractions on FFMA2: measured +16 % at nq = 9, nothing at nq = 7, 8 (profiles/r1_pencil_paired_ab.txt);
-      // BD_PENCIL_PAIRED = 1 / 2 forces it on / off
-      const int pv = pencil_paired_variant();
-      if (full && (pv == 1 || (pv == 0 && NQ == 9)))
-        return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true, true>(a);
-    }
-    if (full)
-      return launch_stiffness_pencil_cfg<T, P, NQ, 1, FULL, true, true, false>(a);
-    if constexpr (sizeof(T) == 8)
-    {
-      // BD_PENCIL_RING = 3: ring of 5 rows restarted per cell (48 KB, still 4 CTAs/SM) -- experiment: ncu puts
-      // 17 % of the fp64 kernel's stall samples on the wait for a G row requested only 2 rows earlier
-      if (ring == 3)
-        return launch_stiffness_pencil_cfg<T, P, NQ, 1, 5, false, false, false>(a);
-    }
-    return launch_stiffness_pencil_cfg<T, P, NQ, 1, 3, false, false, false>(a);
+      return launch_stiffness_pencil_bulk<P, NQ, false>(a);
+    else if constexpr (sizeof(T) == 4)
+      return launch_stiffness_pencil_cfg<T, P, NQ, 1, NQ + 1, true, true, NQ == 9>(a);
+    else
+      return launch_stiffness_pencil_cfg<T, P, NQ, 1, 5, false, false, false>(a);
   }
 }
 

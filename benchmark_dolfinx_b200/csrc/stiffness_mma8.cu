@@ -2,11 +2,10 @@
 #include "stiffness_launch.cuh"
 #include "stiffness_mma8.cuh"
 
-#include <cstdlib>
 
 namespace bd
 {
-template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, int PREFETCH>
+template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 static int launch_mma8(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
@@ -49,24 +48,12 @@ static int launch_mma8(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
-static int env_int(const char* name, int dflt)
-{
-  const char* e = std::getenv(name);
-  return e ? std::atoi(e) : dflt;
-}
-
 template <typename TS, int P, int NQ, bool IDENTITY>
 static int launch_mma8_tuned(const StiffnessArgs& a)
 {
-  // tuning knobs for experiments: BD_MMA8_WARPS (2|4 warps per CTA), BD_MMA8_PREFETCH (0|1|2, see the kernel)
-  static const int warps = env_int("BD_MMA8_WARPS", 4), prefetch = env_int("BD_MMA8_PREFETCH", 1);
-  if (warps == 4)
-  {
-    if (prefetch == 2)
-      return launch_mma8<TS, P, NQ, IDENTITY, 4, 2>(a);
-    return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 4, 1>(a) : launch_mma8<TS, P, NQ, IDENTITY, 4, 0>(a);
-  }
-  return prefetch ? launch_mma8<TS, P, NQ, IDENTITY, 2, 1>(a) : launch_mma8<TS, P, NQ, IDENTITY, 2, 0>(a);
+  // 4 warps per CTA, next cell's dof indices prefetched (measured, round 1).  Prefetching the input values as
+  // well was tried in round 2 and lost by 2.6x (register spills; profiles/r2_experiments_ab.txt): removed.
+  return launch_mma8<TS, P, NQ, IDENTITY, 4, true>(a);
 }
 
 int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const StiffnessArgs& a)

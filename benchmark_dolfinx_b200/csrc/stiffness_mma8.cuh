@@ -113,11 +113,9 @@ __device__ __forceinline__ void mma8_tile(const double (&M)[64], const double (&
   }
 }
 
-// PREFETCH: 0 = nothing, 1 = the next cell's dof indices are loaded while this cell is computed,
-// 2 = its input values too (requested before the transposed interpolation, where few registers are live;
-// experiment, BD_MMA8_PREFETCH=2: ncu puts 13 % of the stall samples of the PREFETCH = 1 kernel on the
-// first DMMA of a cell, waiting for the gathered values).
-template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, int PREFETCH>
+// PREFETCH: the next cell's dof indices are loaded while this cell is computed.  (Prefetching the input values
+// too -- 16 more live doubles -- spilled and ran 2.6x slower: profiles/r2_experiments_ab.txt.)
+template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, bool PREFETCH>
 __global__ void __launch_bounds__(kMma8Warps * 32)
     stiffness_mma8_kernel(const TS* __restrict__ u, TS* __restrict__ y, const TS* __restrict__ Gf,
                           const TS* __restrict__ cell_constants,
@@ -218,12 +216,6 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
         v[yy][s] = valid ? static_cast<double>(u[d[yy][s] & 0x7fffffff]) : 0.0;
       }
   };
-  double nT[PREFETCH == 2 ? 8 : 1][2];
-  if constexpr (PREFETCH == 2)
-  {
-    if (my_cells > 0)
-      load_values(ndof, nT);
-  }
 
   int slot = 0;
   for (int k = 0; k < my_cells; ++k)
@@ -246,26 +238,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       load_dofs(cell_cur, dof);
     // all 16 loads are issued before the first use (a store placed between them would serialise the
     // round trips: the warp stalls in order on the store's operands)
-    if constexpr (PREFETCH == 2)
-    {
-#pragma unroll
-      for (int yy = 0; yy < 8; ++yy)
-#pragma unroll
-        for (int s = 0; s < 2; ++s)
-          T[yy][s] = nT[yy][s];
-    }
-    else
-    {
-#pragma unroll
-      for (int yy = 0; yy < 8; ++yy)
-#pragma unroll
-        for (int s = 0; s < 2; ++s)
-        {
-          const int z = 2 * t + s;
-          const bool valid = (ND == 8) || (g < ND && yy < ND && z < ND);
-          T[yy][s] = valid ? static_cast<double>(u[dof[yy][s] & 0x7fffffff]) : 0.0;
-        }
-    }
+    load_values(dof, T);
     // the next cell's indices travel while this cell is computed
     if (PREFETCH && k + 1 < my_cells)
       load_dofs(cell_next, ndof);
@@ -359,13 +332,6 @@ __global__ void __launch_bounds__(kMma8Warps * 32)
       R[yy][1] = rx1 + rz1;
     }
     mma8_tile<true, true>(tab.dphi, F, R);
-
-    // the next cell's input values (its indices arrived long ago): in flight during the rest of this cell
-    if constexpr (PREFETCH == 2)
-    {
-      if (k + 1 < my_cells)
-        load_values(ndof, nT);
-    }
 
     // ---- transposed interpolation (reference :388-420)
     if constexpr (!IDENTITY)

@@ -30,7 +30,7 @@
 
 #include <cstdint>
 
-#include "stiffness_slab_f2.cuh"
+#include "pair_fma.cuh"
 
 namespace bd
 {
