@@ -40,6 +40,13 @@ def algorithmic_bytes_per_apply(ndofs_local, ncells, degree, nq, tsize):
     return 2 * tsize * ndofs_local + 4 * nd3 * ncells + 6 * tsize * nq ** 3 * ncells + ndofs_local
 
 
+def algorithmic_bytes_per_apply_onthefly(ndofs_local, ncells, nnodes, degree, tsize):
+    """SURVEY.md section 8(d), variant "G on the fly": the G term is replaced by the vertex coordinates
+    (3T per geometry node) and the geometry dofmap (32 bytes per cell)."""
+    nd3 = (degree + 1) ** 3
+    return 2 * tsize * ndofs_local + 4 * nd3 * ncells + 3 * tsize * nnodes + 32 * ncells + ndofs_local
+
+
 def algorithmic_flops_per_cell(degree, nq, qmode):
     nd = degree + 1
     return 2 * (2 * (nq * nd ** 3 + nq ** 2 * nd ** 2 + nq ** 3 * nd)) * qmode + 12 * nq ** 4 + 18 * nq ** 3
@@ -183,6 +190,8 @@ def cpu_reference_run(degree, bits, steps, warmup, target_seconds, cells_per_dim
         steps = max(1, min(steps, int(target_seconds / max(per_step, 1e-9))))
     secs = run_steps(steps)
     gdofs = mesh.ndofs_global * cores * steps / (1e9 * secs)
+    cpu_reference_run.last = {"qmode": 0, "cells_per_instance": [nc, nc, nc], "ndofs_per_instance": int(mesh.ndofs_global),
+                              "instances": cores}
     sample = (f"{cores} independent instances (one per core) of a {nc}x{nc}x{nc}-cell Q{degree} box, "
               f"{mesh.ndofs_global} dofs each, qmode 0 (the reference CPU kernel has no qmode 1), "
               f"fp{bits}, {steps} applies each, {kind} kernel built -O3 -ffast-math")
@@ -199,11 +208,27 @@ def run_reference_arm(args, rank):
         "unit": "GDoF/s", "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * secs / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic",
-        "config": workload_config(args, 1),
+        "config": reference_config(args),
         "cpu_baseline": {"value": gdofs, "unit": "GDoF/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": gdofs, "unit": "GDoF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def reference_config(args):
+    """What the reference arm really ran: the reference CPU kernel supports qmode 0 only
+    (src/laplacian_cpu.hpp:73-74) and its `int` offsets limit the mesh, so the arm runs one small box per core."""
+    r = getattr(cpu_reference_run, "last", {})
+    nc = r.get("cells_per_instance", [0, 0, 0])
+    return {
+        "workload": (f"Q{args.degree} matrix-free Laplacian action on the host CPU, qmode 0 (all the reference CPU kernel "
+                     f"supports), fp{args.float}, {r.get('instances')} independent instances (one per core) of a "
+                     f"{nc[0]}x{nc[1]}x{nc[2]}-cell box with {r.get('ndofs_per_instance')} dofs each; NOT the GPU arm's "
+                     f"qmode {args.qmode} / {args.ndofs}-dofs-per-GPU mesh (the GPU arm reports its own qmode-0 number "
+                     "under gpu_qmode0 for a like-for-like ratio)"),
+        "degree": args.degree, "qmode": 0, "ndofs_per_instance": r.get("ndofs_per_instance"),
+        "instances": r.get("instances"), "cells_per_instance": nc,
+    }
 
 
 def workload_config(args, world):
@@ -219,8 +244,10 @@ def workload_config(args, world):
 
 def reference_gpu_kernel_leg(bd, degree, qmode, dtype, ndofs, steps):
     """GDoF/s of the reference's stiffness_operator_gpu<T,P,Q> (src/laplacian_gpu.hpp:91-426, launched as
-    src/laplacian.hpp:298-306: one CTA of (Q,Q,Q) threads per cell) and of our kernel on the same mesh."""
+    src/laplacian.hpp:298-306: one CTA of (Q,Q,Q) threads per cell) and of our kernels on the same mesh."""
+    import ctypes as C
     import torch
+    from benchmark_dolfinx_b200 import _lib
     from oracle import native
     ref = native.ref_gpu_lib()
     if ref is None:
@@ -228,10 +255,8 @@ def reference_gpu_kernel_leg(bd, degree, qmode, dtype, ndofs, steps):
     bits = 64 if dtype == np.float64 else 32
     n = bd.compute_mesh_size(ndofs, degree)
     mesh = bd.BoxMesh(n, degree, dtype=dtype)
-    op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype)
+    op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, geometry="precomputed")
     t = op.tables
-    import ctypes as C
-    from benchmark_dolfinx_b200 import _lib
     gp, gn = C.c_void_p(), C.c_int64()
     _lib.check(_lib.lib.bd_laplacian_geometry(op._h, C.byref(gp), C.byref(gn)))   # reference-layout copy of G
     tdt = torch.float64 if bits == 64 else torch.float32
@@ -263,14 +288,238 @@ def reference_gpu_kernel_leg(bd, degree, qmode, dtype, ndofs, steps):
     ynorm_ref = bd.norm(y)
     t_ours = timed(lambda: op.apply(u, y))
     ynorm = bd.norm(y)
-    return {"value": mesh.ndofs_global / (1e9 * t_ref), "unit": "GDoF/s", "ms_per_apply": 1e3 * t_ref,
-            "ours_same_mesh": mesh.ndofs_global / (1e9 * t_ours), "speedup": t_ref / t_ours,
-            "ndofs": mesh.ndofs_global, "y_norm_reference_kernel": ynorm_ref, "y_norm_ours": ynorm,
-            "kernel": f"benchdolfinx::stiffness_operator_gpu<{'double' if bits == 64 else 'float'},{degree},{t.nq}> "
-                      "(reference source, unmodified, -arch sm_100a; one CTA per cell)"}
+    out = {"value": mesh.ndofs_global / (1e9 * t_ref), "unit": "GDoF/s", "ms_per_apply": 1e3 * t_ref,
+           "ours_same_mesh_precomputed_G": mesh.ndofs_global / (1e9 * t_ours), "speedup_precomputed_G": t_ref / t_ours,
+           "ndofs": mesh.ndofs_global, "y_norm_reference_kernel": ynorm_ref, "y_norm_ours": ynorm,
+           "rel_diff_y_norm": abs(ynorm - ynorm_ref) / ynorm_ref,
+           "kernel": f"benchdolfinx::stiffness_operator_gpu<{'double' if bits == 64 else 'float'},{degree},{t.nq}> "
+                     "(reference source, unmodified, -arch sm_100a; one CTA per cell)"}
+    del op
+    op2 = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype)            # the default choice
+    if op2.geometry_mode()[0] != "precomputed":
+        t2 = timed(lambda: op2.apply(u, y))
+        out.update(ours_same_mesh_default=mesh.ndofs_global / (1e9 * t2), speedup_default=t_ref / t2,
+                   default_geometry=op2.geometry_mode()[0], y_norm_ours_default=bd.norm(y))
+    return out
 
 
 # ----------------------------------------------------------------------------- our arm
+FP64_PEAK_TFLOPS = 37.1   # DMMA m8n8k4 rate measured on a B200 by scripts/microbench/fp64_rates.cu (DFMA: 34.0)
+
+
+class Ctx:
+    """Per-process plumbing: rank layout, barrier, reductions."""
+
+    def __init__(self, torch, dist, rank, world, comm):
+        self.torch, self.dist, self.rank, self.world, self.comm = torch, dist, rank, world, comm
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def _red(self, v, op):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max(self, v):
+        return self._red(v, self.dist.ReduceOp.MAX if self.world > 1 else None)
+
+    def sum(self, v):
+        return self._red(v, self.dist.ReduceOp.SUM if self.world > 1 else None)
+
+
+def load_traffic(degree, qmode, bits, mode, ncells):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture, scaled to this mesh."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            tr = json.load(f)
+        key = f"q{degree}_qmode{qmode}_f{bits}" + ("" if mode == "precomputed" else "_onthefly")
+        if key in tr and tr[key].get("ncells"):
+            return tr[key]["dram_bytes_per_launch"] * (ncells / tr[key]["ncells"])
+    except Exception:
+        pass
+    return None
+
+
+def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, sample_clocks=False, local_rank=0):
+    """W warm-up + K timed operator applications; roofline of the stiffness kernel from per-launch events."""
+    torch = ctx.torch
+    tsize = bits // 8
+    nq = degree + 1 + qmode
+    for _ in range(warmup):
+        op.apply(u, y)
+    ctx.barrier()
+    sampler = ClockSampler(local_rank) if (sample_clocks and ctx.rank == 0) else None
+    op.profile(True)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        op.apply(u, y)
+    ev1.record()
+    ctx.barrier()
+    secs = ctx.max(ev0.elapsed_time(ev1) / 1e3)
+    kernel_ms, kernel_launches = op.profile_read()
+    op.profile(False)
+    clocks = sampler.stop() if sampler is not None else None
+    mode = op.geometry_mode()[0]
+    peak, peak_src = measured_peak_gbs()
+    if mode == "precomputed":
+        bytes_apply = algorithmic_bytes_per_apply(mesh.ndofs_local, mesh.ncells, degree, nq, tsize)
+    else:
+        bytes_apply = algorithmic_bytes_per_apply_onthefly(mesh.ndofs_local, mesh.ncells, mesh.nnodes, degree, tsize)
+    kernel_s = ctx.max(kernel_ms / 1e3 / steps)
+    achieved = bytes_apply / kernel_s / 1e9
+    gflops = algorithmic_flops_per_cell(degree, nq, qmode) * mesh.ncells / kernel_s / 1e9
+    roofline = {
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": load_traffic(degree, qmode, bits, mode, mesh.ncells), "peak_source": peak_src,
+        "frac_of_8TBs_nominal": achieved / 8000.0, "kernel": op.describe(), "geometry": mode,
+        "kernel_ms_per_apply": 1e3 * kernel_s, "kernel_launches_per_apply": kernel_launches // steps,
+        "algorithmic_bytes_per_apply": bytes_apply, "algorithmic_bytes_per_dof": bytes_apply / mesh.ndofs_local,
+        "fp_gflops_algorithmic": gflops,
+    }
+    if bits == 64:
+        roofline["fp64_pipe"] = {"achieved_tflops_algorithmic": gflops / 1e3, "peak_tflops": FP64_PEAK_TFLOPS,
+                                 "frac": gflops / 1e3 / FP64_PEAK_TFLOPS,
+                                 "peak_source": "scripts/microbench/fp64_rates.cu on a B200 (round 1): DMMA 37.1, DFMA 34.0"}
+    if mode != "precomputed":
+        roofline["note"] = ("geometry on the fly: no G stream, the kernel is bound by the fp64 pipe (fp64_pipe), not by "
+                            "HBM; `frac` is still its algorithmic bytes over the HBM peak")
+    return {"value": mesh.ndofs_global * steps / (1e9 * secs), "ms_per_step": 1e3 * secs / steps, "secs": secs,
+            "roofline": roofline, "clocks": clocks, "launches": kernel_launches, "geometry": mode}
+
+
+def cg_leg(ctx, bd, mesh, op, u, steps, warmup, bytes_apply, tsize):
+    """`steps` CG iterations (timed region includes the initial apply, as src/cg.hpp:108)."""
+    torch = ctx.torch
+    x = torch.zeros_like(u)
+    bd.cg_solve(op, x, u, max(1, warmup), 0.0, ctx.comm)
+    ctx.barrier()
+    x.zero_()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    its = bd.cg_solve(op, x, u, steps, 0.0, ctx.comm)
+    c1.record()
+    ctx.barrier()
+    cg_secs = ctx.max(c0.elapsed_time(c1) / 1e3)
+    return {"value": mesh.ndofs_global * its / (1e9 * cg_secs), "unit": "GDoF/s", "iterations": its,
+            "ms_per_iter": 1e3 * cg_secs / its, "x_norm": bd.norm(x, mesh.ndofs_owned, ctx.comm),
+            "hbm_gbs_algorithmic": (bytes_apply * (its + 1) + 11 * tsize * mesh.ndofs_local * its) / cg_secs / 1e9,
+            "geometry": op.geometry_mode()[0],
+            "note": "timed region = initial apply + iterations, as the reference's cg_solve"}
+
+
+def parity_leg(ctx, bd, geometry):
+    """Known answers of the reference through the SAME communicator / partition as the timed legs:
+    examples/mat_comp-16.json (Q3, qmode 1, 100 048 dofs: u_norm, y_norm), src/test_output.py:19 (Q3, qmode 0,
+    1000 dofs: y_norm) and a 10 000-dof 50-iteration CG whose answer is pinned by the oracle's CG
+    (tests/test_gpu_nccl.py).  Norms are partition independent."""
+    torch = ctx.torch
+    out = {}
+    worst = 0.0
+    for name, ndofs, qmode, unorm_ref, ynorm_ref in (
+            ("mat_comp_16", 100000, 1, 0.6895773850559623, 0.14150257625641838),
+            ("test_output", 1000, 0, None, 9.912865833415553)):
+        n = bd.compute_mesh_size(ndofs, 3)
+        mesh = bd.BoxMesh(n, 3, ctx.rank, ctx.world)
+        halo = bd.Halo(ctx.comm, mesh) if ctx.world > 1 else None
+        for geo in sorted({"precomputed", geometry}):
+            op = bd.MatFreeLaplacianGPU(mesh, 3, qmode, 2.0, halo=halo, geometry=geo)
+            u = mesh.assemble_rhs(qmode)
+            y = torch.zeros_like(u)
+            op.apply(u, y)
+            ynorm = bd.norm(y, mesh.ndofs_owned, ctx.comm)
+            err = abs(ynorm - ynorm_ref) / ynorm_ref
+            if unorm_ref is not None:
+                err = max(err, abs(bd.norm(u, mesh.ndofs_owned, ctx.comm) - unorm_ref) / unorm_ref)
+            out[f"{name}_{op.geometry_mode()[0]}"] = {"y_norm": ynorm, "expected": ynorm_ref, "rel_err": err}
+            worst = max(worst, err)
+    n = bd.compute_mesh_size(10000, 3)
+    mesh = bd.BoxMesh(n, 3, ctx.rank, ctx.world)
+    halo = bd.Halo(ctx.comm, mesh) if ctx.world > 1 else None
+    op = bd.MatFreeLaplacianGPU(mesh, 3, 1, 2.0, halo=halo, geometry=geometry)
+    u = mesh.assemble_rhs(1)
+    x = torch.zeros_like(u)
+    its = bd.cg_solve(op, x, u, 50, 0.0, ctx.comm)
+    xnorm = bd.norm(x, mesh.ndofs_owned, ctx.comm)
+    cg_ref = 167.59244725655134
+    cg_err = abs(xnorm - cg_ref) / cg_ref
+    out["cg_50_10000dofs"] = {"x_norm": xnorm, "expected": cg_ref, "rel_err": cg_err, "iterations": its}
+    out["rel_err"] = worst
+    out["cg_rel_err"] = cg_err
+    out["tolerance"] = 1e-12
+    out["cg_tolerance"] = 1e-11     # 50 iterations amplify the summation-order differences between partitions
+    out["ok"] = bool(worst <= 1e-12 and cg_err <= 1e-11 and its == 50)
+    return out
+
+
+def e2e_leg(ctx, mesh, op, u, steps, tsize):
+    """End to end through the host-buffer C-ABI call: H2D u, (halo +) apply, D2H y every step."""
+    torch = ctx.torch
+    uh = torch.empty(mesh.ndofs_local, dtype=u.dtype, pin_memory=True)
+    yh = [torch.empty(mesh.ndofs_local, dtype=u.dtype, pin_memory=True) for _ in range(2)]
+    uh.copy_(u)
+    torch.cuda.synchronize()
+    uh_np, yh_np = uh.numpy(), [t.numpy() for t in yh]
+    e_steps = max(2, min(steps, 20))
+    s_steps = max(2, min(steps, 4))
+    op.apply_host(uh_np, yh_np[0])                        # warm-up (allocates staging)
+    op.apply_host_batch([uh_np, uh_np], yh_np)
+    ctx.barrier()
+    # (a) one synchronous call per step: H2D, apply, D2H strictly in sequence
+    t0 = time.perf_counter()
+    for _ in range(s_steps):
+        op.apply_host(uh_np, yh_np[0])
+    torch.cuda.synchronize()
+    seq_local = time.perf_counter() - t0
+    seq_secs = ctx.max(seq_local)
+    ctx.barrier()
+    # (b) the batch call: every step still copies its input in and its result out, but the copies of
+    #     neighbouring steps overlap with the operator (PCIe is full duplex)
+    t0 = time.perf_counter()
+    op.apply_host_batch([uh_np] * e_steps, [yh_np[i & 1] for i in range(e_steps)])
+    torch.cuda.synchronize()
+    e_local = time.perf_counter() - t0
+    e_secs = ctx.max(e_local)
+    ctx.barrier()
+    bytes_rank = mesh.ndofs_local * tsize
+    rate_local = bytes_rank * e_steps / e_local / 1e9
+    rate_min = -ctx.max(-rate_local)
+    rate_max = ctx.max(rate_local)
+    ndg = mesh.ndofs_global
+    return {"value": ndg * e_steps / (1e9 * e_secs), "unit": "GDoF/s",
+            "h2d_bytes_per_step": int(ctx.sum(bytes_rank)), "d2h_bytes_per_step": int(ctx.sum(bytes_rank)),
+            "steps": e_steps, "ms_per_step": 1e3 * e_secs / e_steps, "geometry": op.geometry_mode()[0],
+            "per_rank_copy_gbs_each_way": {"min": rate_min, "max": rate_max,
+                                           "note": "bytes of one direction / wall time of the pipelined call, per rank"},
+            "call": "bd_laplacian_apply_host_batch (pinned host in/out vectors; H2D, operator and D2H of "
+                    "consecutive steps pipelined on three streams)",
+            "sequential": {"value": ndg * s_steps / (1e9 * seq_secs), "ms_per_step": 1e3 * seq_secs / s_steps,
+                           "steps": s_steps, "call": "bd_laplacian_apply_host, one synchronous call per step"},
+            "y_norm_host": float(np.linalg.norm(yh_np[(e_steps - 1) & 1][:mesh.ndofs_owned].astype(np.float64)))
+            if ctx.world == 1 else None}
+
+
+def build_case(ctx, bd, degree, qmode, dtype, ndofs_per_rank, ndofs_global, geometry):
+    """Mesh, halo plan, operator and input vector of one configuration (global box as src/main.cpp:237-240,272-273)."""
+    torch = ctx.torch
+    n = bd.compute_mesh_size(ndofs_global or ndofs_per_rank * ctx.world, degree)
+    t0 = time.perf_counter()
+    mesh = bd.BoxMesh(n, degree, ctx.rank, ctx.world, dtype=dtype)
+    halo = bd.Halo(ctx.comm, mesh) if ctx.world > 1 else None
+    op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, halo=halo, geometry=geometry)
+    u = mesh.assemble_rhs(qmode)
+    y = torch.zeros_like(u)
+    if halo is not None:
+        halo.scatter_fwd(u)
+    torch.cuda.synchronize()
+    return n, mesh, halo, op, u, y, time.perf_counter() - t0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -283,13 +532,20 @@ def main():
                     help="fixed global size (strong scaling, reference --ndofs_global); overrides --ndofs")
     ap.add_argument("--float", type=int, default=64, choices=[32, 64])
     ap.add_argument("--qmode", type=int, default=1, choices=[0, 1])
-    ap.add_argument("--no-cg", action="store_true", help="skip the CG leg")
+    ap.add_argument("--geometry", default="auto", choices=["auto", "precomputed", "onthefly"],
+                    help="geometry variant of the headline legs: G precomputed and streamed (what the reference does), "
+                         "rebuilt on the fly in the stiffness kernel, or auto = the operator's own choice (on the fly "
+                         "when every cell is a parallelepiped).  The other variant is measured too and reported "
+                         "under `variants`")
+    ap.add_argument("--no-cg", action="store_true", help="skip the CG legs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
-    ap.add_argument("--reference-gpu-kernel", action="store_true",
-                    help="also time the reference's own CUDA kernel (oracle/_ref/libref_gpu.so, test "
-                         "infrastructure) on this GPU; off by default: the default run executes nothing "
-                         "under oracle/ except the CPU baseline")
+    ap.add_argument("--no-variants", action="store_true", help="skip the legs of the other geometry variant")
+    ap.add_argument("--no-q6", action="store_true", help="skip the Q6 / 500M-dof sub-record")
+    ap.add_argument("--no-parity", action="store_true", help="skip the known-answer parity leg")
+    ap.add_argument("--no-reference-gpu-kernel", action="store_true",
+                    help="skip timing the reference's own CUDA kernel (oracle/_ref/libref_gpu.so, test "
+                         "infrastructure, the kernel to beat of SURVEY.md section 8d)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -312,157 +568,103 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     comm = bd.Comm.from_torch_distributed() if world > 1 else None
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    ctx = Ctx(torch, dist, rank, world, comm)
 
     dtype = np.float64 if args.float == 64 else np.float32
     tsize = args.float // 8
     degree, qmode = args.degree, args.qmode
     if args.ndofs_global:                                          # src/main.cpp:237-240
         args.ndofs = args.ndofs_global // world
-    n = bd.compute_mesh_size(args.ndofs_global or args.ndofs * world, degree)   # src/main.cpp:272-273
-    t_setup = time.perf_counter()
-    mesh = bd.BoxMesh(n, degree, rank, world, dtype=dtype)
-    halo = bd.Halo(comm, mesh) if world > 1 else None
-    op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, halo=halo)
-    u = mesh.assemble_rhs(qmode)
-    y = torch.zeros_like(u)
-    if halo is not None:
-        halo.scatter_fwd(u)
-    torch.cuda.synchronize()
-    t_setup = time.perf_counter() - t_setup
-    ndofs_global = mesh.ndofs_global
-    nq = degree + 1 + qmode
 
-    # ---- operator action: W warm-up + K timed steps
-    for _ in range(args.warmup):
-        op.apply(u, y)
-    barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    op.profile(True)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(args.steps):
-        op.apply(u, y)
-    ev1.record()
-    barrier()
-    secs = max_over_ranks(ev0.elapsed_time(ev1) / 1e3)
-    kernel_ms, kernel_launches = op.profile_read()
-    op.profile(False)
-    clocks = sampler.stop() if sampler is not None else None
-    value = ndofs_global * args.steps / (1e9 * secs)
+    # ---- known answers through this communicator, before anything is timed
+    parity = None
+    if not args.no_parity:
+        parity = parity_leg(ctx, bd, args.geometry)
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"error": "parity leg failed", "parity": parity}), flush=True)
+            raise SystemExit(3)
+
+    # ---- headline legs: operator action, CG, end to end
+    n, mesh, halo, op, u, y, t_setup = build_case(ctx, bd, degree, qmode, dtype, args.ndofs, args.ndofs_global,
+                                                  args.geometry)
+    ndofs_global = mesh.ndofs_global
+    head = action_leg(ctx, bd, mesh, op, u, y, args.steps, args.warmup, degree, qmode, args.float,
+                      sample_clocks=True, local_rank=local_rank)
     unorm = bd.norm(u, mesh.ndofs_owned, comm)
     ynorm = bd.norm(y, mesh.ndofs_owned, comm)
-
-    # ---- roofline of the dominant kernel (stiffness), from the per-launch events
-    peak, peak_src = measured_peak_gbs()
-    bytes_apply = algorithmic_bytes_per_apply(mesh.ndofs_local, mesh.ncells, degree, nq, tsize)
-    kernel_s_per_apply = max_over_ranks(kernel_ms / 1e3 / args.steps)
-    achieved = bytes_apply / kernel_s_per_apply / 1e9
-    launches_per_apply = kernel_launches // args.steps
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
-            tr = json.load(f)
-        key = f"q{degree}_qmode{qmode}_f{args.float}"
-        if key in tr and tr[key].get("ncells"):
-            traffic = tr[key]["dram_bytes_per_launch"] * (mesh.ncells / tr[key]["ncells"])
-    except Exception:
-        pass
-    roofline = {
-        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
-        "kernel": op.describe(),
-        "kernel_ms_per_apply": 1e3 * kernel_s_per_apply, "kernel_launches_per_apply": launches_per_apply,
-        "algorithmic_bytes_per_apply": bytes_apply,
-        "algorithmic_bytes_per_dof": bytes_apply / mesh.ndofs_local,
-        "fp_gflops_algorithmic": algorithmic_flops_per_cell(degree, nq, qmode) * mesh.ncells
-                                 / kernel_s_per_apply / 1e9,
-    }
-
-    # ---- CG: `steps` iterations (timed region includes the initial apply, as src/cg.hpp:108)
-    cg = None
+    launches_per_apply = head["roofline"]["kernel_launches_per_apply"]
     gpu_launches = args.steps * launches_per_apply + (args.steps if world > 1 else 0)
-    if not args.no_cg:
-        x = torch.zeros_like(u)
-        bd.cg_solve(op, x, u, max(1, args.warmup), 0.0, comm)
-        barrier()
-        x.zero_()
-        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        c0.record()
-        its = bd.cg_solve(op, x, u, args.steps, 0.0, comm)
-        c1.record()
-        barrier()
-        cg_secs = max_over_ranks(c0.elapsed_time(c1) / 1e3)
-        cg = {"value": ndofs_global * its / (1e9 * cg_secs), "unit": "GDoF/s", "iterations": its,
-              "ms_per_iter": 1e3 * cg_secs / its, "x_norm": bd.norm(x, mesh.ndofs_owned, comm),
-              "hbm_gbs_algorithmic": (bytes_apply * (its + 1) + 11 * tsize * mesh.ndofs_local * its)
-                                     / cg_secs / 1e9,
-              "note": "timed region = initial apply + iterations, as the reference's cg_solve"}
-        del x
+    bytes_apply = head["roofline"]["algorithmic_bytes_per_apply"]
+    cg = None if args.no_cg else cg_leg(ctx, bd, mesh, op, u, args.steps, args.warmup, bytes_apply, tsize)
+    e2e = None if args.no_e2e else e2e_leg(ctx, mesh, op, u, args.steps, tsize)
+    head_mode = head["geometry"]
+    del op
 
-    # ---- end to end through the host-buffer C-ABI call: H2D u, (halo +) apply, D2H y every step
-    e2e = None
-    if not args.no_e2e:
-        uh = torch.empty(mesh.ndofs_local, dtype=u.dtype, pin_memory=True)
-        yh = [torch.empty(mesh.ndofs_local, dtype=u.dtype, pin_memory=True) for _ in range(2)]
-        uh.copy_(u)
-        torch.cuda.synchronize()
-        uh_np, yh_np = uh.numpy(), [t.numpy() for t in yh]
-        e_steps = max(2, min(args.steps, 20))
-        s_steps = max(2, min(args.steps, 4))
-        op.apply_host(uh_np, yh_np[0])                        # warm-up (allocates staging)
-        op.apply_host_batch([uh_np, uh_np], yh_np)
-        barrier()
-        # (a) one synchronous call per step: H2D, apply, D2H strictly in sequence
-        t0 = time.perf_counter()
-        for _ in range(s_steps):
-            op.apply_host(uh_np, yh_np[0])
-        torch.cuda.synchronize()
-        seq_secs = max_over_ranks(time.perf_counter() - t0)
-        barrier()
-        # (b) the batch call: every step still copies its input in and its result out, but the
-        #     copies of neighbouring steps overlap with the operator (PCIe is full duplex)
-        t0 = time.perf_counter()
-        op.apply_host_batch([uh_np] * e_steps, [yh_np[i & 1] for i in range(e_steps)])
-        torch.cuda.synchronize()
-        e_secs = max_over_ranks(time.perf_counter() - t0)
-        barrier()
-        e2e = {"value": ndofs_global * e_steps / (1e9 * e_secs), "unit": "GDoF/s",
-               "h2d_bytes_per_step": int(sum_over_ranks(mesh.ndofs_local * tsize)),
-               "d2h_bytes_per_step": int(sum_over_ranks(mesh.ndofs_local * tsize)),
-               "steps": e_steps, "ms_per_step": 1e3 * e_secs / e_steps,
-               "call": "bd_laplacian_apply_host_batch (pinned host in/out vectors; H2D, operator and D2H of "
-                       "consecutive steps pipelined on three streams)",
-               "sequential": {"value": ndofs_global * s_steps / (1e9 * seq_secs),
-                              "ms_per_step": 1e3 * seq_secs / s_steps, "steps": s_steps,
-                              "call": "bd_laplacian_apply_host, one synchronous call per step"},
-               "y_norm_host": float(np.linalg.norm(yh_np[(e_steps - 1) & 1][:mesh.ndofs_owned].astype(np.float64)))
-               if world == 1 else None}
-        del uh, yh
+    # ---- the other geometry variant on the same mesh (both are part of the measurement)
+    variants = {head_mode: {"value": head["value"], "ms_per_step": head["ms_per_step"], "roofline": head["roofline"],
+                            "cg": cg and cg["value"], "y_norm": ynorm, "headline": True}}
+    if not args.no_variants:
+        other = "precomputed" if head_mode != "precomputed" else "onthefly"
+        try:
+            op2 = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, halo=halo, geometry=other)
+            leg = action_leg(ctx, bd, mesh, op2, u, y, args.steps, args.warmup, degree, qmode, args.float)
+            yn2 = bd.norm(y, mesh.ndofs_owned, comm)
+            cg2 = None if args.no_cg else cg_leg(ctx, bd, mesh, op2, u, args.steps, args.warmup,
+                                                 leg["roofline"]["algorithmic_bytes_per_apply"], tsize)
+            variants[leg["geometry"]] = {"value": leg["value"], "ms_per_step": leg["ms_per_step"],
+                                         "roofline": leg["roofline"], "cg": cg2 and cg2["value"], "y_norm": yn2,
+                                         "rel_diff_y_norm_vs_headline": abs(yn2 - ynorm) / ynorm, "headline": False}
+            gpu_launches += args.steps * leg["roofline"]["kernel_launches_per_apply"]
+            del op2
+        except bd.BenchDolfinxError as exc:
+            variants[other] = {"value": None, "note": str(exc)}
+
+    # ---- the GPU at qmode 0, beside the qmode-0 CPU baseline
+    gpu_q0 = None
+    if qmode != 0 and world == 1 and not args.no_cpu:
+        del mesh, halo, u, y
+        _, mesh0, halo0, op0, u0, y0, _ = build_case(ctx, bd, degree, 0, dtype, args.ndofs, args.ndofs_global,
+                                                     args.geometry)
+        leg = action_leg(ctx, bd, mesh0, op0, u0, y0, max(3, args.steps // 2), args.warmup, degree, 0, args.float)
+        gpu_q0 = {"value": leg["value"], "unit": "GDoF/s", "ms_per_step": leg["ms_per_step"],
+                  "roofline_frac": leg["roofline"]["frac"], "geometry": leg["geometry"], "kernel": leg["roofline"]["kernel"],
+                  "note": "same mesh and degree at qmode 0, the only mode the reference CPU kernel supports"}
+        del op0, mesh0, halo0, u0, y0
+    else:
+        del mesh, halo, u, y
+    torch.cuda.empty_cache()
+
+    # ---- Q6 at 500M dofs per GPU: the other half of BASELINE.json's metric ("Q3/Q6")
+    q6 = None
+    default_headline = (degree == 3 and qmode == 1 and args.float == 64 and not args.ndofs_global
+                        and args.ndofs == 300_000_000)
+    if default_headline and not args.no_q6:
+        n6, mesh6, halo6, op6, u6, y6, t6 = build_case(ctx, bd, 6, 1, np.float64, 500_000_000, 0, args.geometry)
+        leg = action_leg(ctx, bd, mesh6, op6, u6, y6, args.steps, args.warmup, 6, 1, 64)
+        q6 = {"value": leg["value"], "unit": "GDoF/s", "ms_per_step": leg["ms_per_step"], "roofline": leg["roofline"],
+              "geometry": leg["geometry"], "ndofs_global": mesh6.ndofs_global, "mesh_cells": n6, "setup_seconds": t6,
+              "y_norm": bd.norm(y6, mesh6.ndofs_owned, comm),
+              "cg": None if args.no_cg else cg_leg(ctx, bd, mesh6, op6, u6, args.steps, args.warmup,
+                                                   leg["roofline"]["algorithmic_bytes_per_apply"], 8)}
+        gpu_launches += args.steps * leg["roofline"]["kernel_launches_per_apply"]
+        if not args.no_variants:
+            other = "precomputed" if leg["geometry"] != "precomputed" else "onthefly"
+            del op6
+            op6 = bd.MatFreeLaplacianGPU(mesh6, 6, 1, 2.0, halo=halo6, geometry=other)
+            leg2 = action_leg(ctx, bd, mesh6, op6, u6, y6, args.steps, args.warmup, 6, 1, 64)
+            q6["variants"] = {leg["geometry"]: {"value": leg["value"], "roofline_frac": leg["roofline"]["frac"]},
+                              leg2["geometry"]: {"value": leg2["value"], "ms_per_step": leg2["ms_per_step"],
+                                                 "roofline": leg2["roofline"],
+                                                 "y_norm": bd.norm(y6, mesh6.ndofs_owned, comm)}}
+        del op6, mesh6, halo6, u6, y6
+        torch.cuda.empty_cache()
 
     # ---- the kernel to beat: the reference's own stiffness_operator_gpu (unmodified source recompiled for
     #      sm_100a, oracle/_ref/libref_gpu.so) with its own launch shape, on a smaller mesh of the same
     #      degree (its G layout needs a second copy of G), timed with CUDA events on the same GPU
     ref_gpu = None
-    if world == 1 and rank == 0 and args.reference_gpu_kernel:
+    if world == 1 and rank == 0 and not args.no_reference_gpu_kernel:
         try:
             ref_gpu = reference_gpu_kernel_leg(bd, degree, qmode, dtype, min(args.ndofs, 100_000_000),
                                                max(3, min(args.steps, 10)))
@@ -480,18 +682,18 @@ def main():
                    "sample": f"{type(exc).__name__}: {exc}"}
 
     if rank == 0:
+        cfg = dict(workload_config(args, world), ndofs_global_requested=args.ndofs_global or None, mesh_cells=n,
+                   ndofs_global=ndofs_global, setup_seconds=t_setup, geometry=head_mode,
+                   geometry_requested=args.geometry)
         line = {
-            "metric": "gdof_per_second_laplacian_action", "value": value, "unit": "GDoF/s",
+            "metric": "gdof_per_second_laplacian_action", "value": head["value"], "unit": "GDoF/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True,
+            "ms_per_step": head["ms_per_step"], "higher_is_better": True,
             "scaling": "strong" if args.ndofs_global else "weak",
-            "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic",
-            "config": dict(workload_config(args, world), ndofs_global_requested=args.ndofs_global or None, mesh_cells=n, ndofs_global=ndofs_global,
-                           ncells_global=mesh.ncells_global, setup_seconds=t_setup),
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cg": cg,
-            "reference_gpu_kernel": ref_gpu,
-            "gpu_launches": gpu_launches, "clocks": clocks,
-            "u_norm": unorm, "y_norm": ynorm,
+            "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic", "config": cfg,
+            "roofline": head["roofline"], "cpu_baseline": cpu, "gpu_qmode0": gpu_q0, "e2e": e2e, "cg": cg,
+            "variants": variants, "q6": q6, "parity": parity, "reference_gpu_kernel": ref_gpu,
+            "gpu_launches": gpu_launches, "clocks": head["clocks"], "u_norm": unorm, "y_norm": ynorm,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -305,7 +305,13 @@ class MatFreeLaplacianGPU:
     ``cell_dofmap, xgeom, geometry_dofmap, bc_marker, lcells, bcells`` attributes)."""
 
     def __init__(self, mesh, degree: int, qmode: int, constant: float, use_gauss: bool = False,
-                 dtype=np.float64, halo: Halo | None = None, tables: Tables | None = None):
+                 dtype=np.float64, halo: Halo | None = None, tables: Tables | None = None,
+                 geometry: str = "auto"):
+        """``geometry``: "precomputed" = G stored and streamed as the reference does
+        (src/laplacian.hpp:238-272), "onthefly" = G rebuilt inside the stiffness kernel from the cell
+        vertices, "auto" (default) = on the fly when every cell is a parallelepiped, precomputed otherwise."""
+        if geometry not in ("auto", "precomputed", "onthefly"):
+            raise BenchDolfinxError(-1, "geometry must be 'auto', 'precomputed' or 'onthefly'")
         self.bits = _bits(dtype)
         self.value_type = _np_dtype(self.bits)
         self.degree, self.qmode = int(degree), int(qmode)
@@ -343,6 +349,8 @@ class MatFreeLaplacianGPU:
                 setattr(d, k, _ptr(v))
             d.flags = 0
             self.n_owned = getattr(mesh, "ndofs_owned", d.ndofs)
+        d.flags |= {"auto": 0, "onthefly": _lib.BD_FLAG_GEOMETRY_ONTHEFLY,
+                    "precomputed": _lib.BD_FLAG_GEOMETRY_PRECOMPUTED}[geometry]
         d.phi0, d.dphi1 = _ptr(t.phi0), _ptr(t.dphi1)
         d.weights, d.dphi_geometry = _ptr(t.weights3d), _ptr(t.dphi_geometry)
         self.ndofs = int(d.ndofs)
@@ -387,6 +395,12 @@ class MatFreeLaplacianGPU:
         pout = (C.c_void_p * n)(*[_ptr(b) for b in outs])
         halo = self.halo._h if self.halo is not None else None
         check(lib.bd_laplacian_apply_host_batch(self._h, halo, n, pin, pout))
+
+    def geometry_mode(self):
+        """("precomputed" | "onthefly-affine" | "onthefly-general", number of non-affine cells or -1)."""
+        mode, n = C.c_int(), C.c_int64()
+        check(lib.bd_laplacian_geometry_mode(self._h, C.byref(mode), C.byref(n)))
+        return ("precomputed", "onthefly-affine", "onthefly-general")[mode.value], n.value
 
     def describe(self) -> str:
         buf = C.create_string_buffer(256)

@@ -14,6 +14,8 @@ LIB_PATH = os.path.join(_HERE, "libbenchdolfinx_b200.so")
 
 BD_SUCCESS = 0
 BD_FLAG_BORROW_DEVICE_ARRAYS = 1
+BD_FLAG_GEOMETRY_ONTHEFLY = 2
+BD_FLAG_GEOMETRY_PRECOMPUTED = 4
 BD_UNIQUE_ID_BYTES = 128
 
 
@@ -78,6 +80,7 @@ PROTOTYPES = {
     "bd_laplacian_apply_host": (C.c_int, [_V, _V, _V, _V]),
     "bd_laplacian_apply_host_batch": (C.c_int, [_V, _V, C.c_int, _V, _V]),
     "bd_laplacian_profile": (C.c_int, [_V, C.c_int]),
+    "bd_laplacian_geometry_mode": (C.c_int, [_V, C.POINTER(C.c_int), C.POINTER(C.c_int64)]),
     "bd_laplacian_describe": (C.c_int, [_V, C.c_char_p, C.c_size_t]),
     "bd_laplacian_profile_read": (C.c_int, [_V, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "bd_laplacian_geometry": (C.c_int, [_V, C.POINTER(_V), C.POINTER(C.c_int64)]),

@@ -4,6 +4,7 @@
 #include "operator.cuh"
 #include "stiffness_launch.cuh"
 
+#include <cmath>
 #include <cstring>
 
 using namespace bd;
@@ -20,6 +21,101 @@ int check_device_available()
     return fail(BD_ERR_NO_DEVICE, "no usable CUDA device (%s); this library has no CPU fallback",
                 e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
   }
+  return BD_SUCCESS;
+}
+
+// Recover the 1-D quadrature rule from the 3-D tables the caller supplied (weights[nq^3], dphi_geometry
+// [3][nq^3][8]) and check that they have the structure the on-the-fly kernels assume: tensor-product weights,
+// trilinear coordinate element with vertex v = 4a + 2b + c, point q = (q0 nq + q1) nq + q2 (the reference gets
+// both from Basix, src/laplacian.hpp:144-169).  Leaves op->w1d / op->pts1d empty when the tables do not fit.
+template <typename T>
+void recover_1d_rule(bd_laplacian* op, const std::vector<char>& wbuf, const std::vector<char>& dbuf)
+{
+  const int nq = op->nq, nq2 = nq * nq, nq3 = nq2 * nq;
+  const T* w3 = reinterpret_cast<const T*>(wbuf.data());
+  const T* dphi = reinterpret_cast<const T*>(dbuf.data());
+  auto D = [&](int d, int q, int v) { return static_cast<double>(dphi[(static_cast<size_t>(d) * nq3 + q) * 8 + v]); };
+  std::vector<double> w(nq), x(nq);
+  double wsum = 0;
+  for (int q = 0; q < nq3; ++q)
+    wsum += static_cast<double>(w3[q]);
+  for (int a = 0; a < nq; ++a)
+  {
+    double s = 0;
+    for (int r = 0; r < nq2; ++r)
+      s += static_cast<double>(w3[a * nq2 + r]);
+    w[a] = s / (wsum > 0 ? std::cbrt(wsum) * std::cbrt(wsum) : 1.0); // sum over the other two directions
+    // d/dxi1 of vertex (a=1,b=1,c=*) summed over c = xi0 at the point; take a point with q0 = a
+    x[a] = D(1, a * nq2, 6) + D(1, a * nq2, 7);
+  }
+  const double tol = sizeof(T) == 8 ? 1e-12 : 2e-5;
+  bool ok = wsum > 0;
+  for (int q0 = 0; q0 < nq && ok; ++q0)
+    for (int q1 = 0; q1 < nq && ok; ++q1)
+      for (int q2 = 0; q2 < nq && ok; ++q2)
+      {
+        const int q = (q0 * nq + q1) * nq + q2;
+        if (std::fabs(static_cast<double>(w3[q]) - w[q0] * w[q1] * w[q2]) > tol * wsum)
+          ok = false;
+        const double xi[3] = {x[q0], x[q1], x[q2]};
+        for (int v = 0; v < 8 && ok; ++v)
+        {
+          const int abc[3] = {(v >> 2) & 1, (v >> 1) & 1, v & 1};
+          for (int d = 0; d < 3 && ok; ++d)
+          {
+            double e = 1;
+            for (int k = 0; k < 3; ++k)
+              e *= (k == d) ? (abc[k] ? 1.0 : -1.0) : (abc[k] ? xi[k] : 1.0 - xi[k]);
+            if (std::fabs(D(d, q, v) - e) > tol)
+              ok = false;
+          }
+        }
+      }
+  if (ok)
+  {
+    op->w1d = w;
+    op->pts1d = x;
+  }
+}
+
+template <typename T>
+int count_nonaffine(bd_laplacian* op)
+{
+  const std::int64_t n = op->n_lcells + op->n_bcells;
+  op->n_nonaffine = 0;
+  if (n == 0)
+    return BD_SUCCESS;
+  unsigned long long* cnt = nullptr;
+  BD_CUDA_CHECK(cudaMalloc(&cnt, sizeof(unsigned long long)));
+  cudaMemset(cnt, 0, sizeof(unsigned long long));
+  const std::int64_t want = (n + 255) / 256;
+  const std::int64_t cap = static_cast<std::int64_t>(sm_count()) * 8;
+  count_nonaffine_kernel<T><<<static_cast<int>(want < cap ? want : cap), 256>>>(
+      reinterpret_cast<const T*>(op->xgeom.ptr), op->geometry_dofmap.ptr, op->cell_list.ptr, n, cnt);
+  unsigned long long h = 0;
+  const cudaError_t e = cudaMemcpy(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost);
+  cudaFree(cnt);
+  if (e != cudaSuccess)
+    return fail(BD_ERR_CUDA, "affine-cell count failed: %s", cudaGetErrorString(e));
+  op->n_nonaffine = static_cast<std::int64_t>(h);
+  return BD_SUCCESS;
+}
+
+// G for the whole list in the layout of the stored-G kernels (no-op for the on-the-fly variants).
+int precompute_geometry(bd_laplacian* op)
+{
+  const size_t ts = op->scalar_size();
+  op->g_layout = preferred_g_layout(op->scalar_bits, op->degree, op->nq);
+  op->g_bcells_offset = g_layout_size(op->g_layout, op->nq, op->n_lcells);
+  const std::int64_t g_total = op->g_bcells_offset + g_layout_size(op->g_layout, op->nq, op->n_bcells);
+  BD_CHECK(op->G.alloc(static_cast<size_t>(g_total > 0 ? g_total : 1) * ts));
+  BD_CHECK(geometry_compute_layout(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                                   op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, op->n_lcells,
+                                   op->G.ptr, nullptr, op->g_layout));
+  BD_CHECK(geometry_compute_layout(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                                   op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr + op->n_lcells,
+                                   op->n_bcells, op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts,
+                                   nullptr, op->g_layout));
   return BD_SUCCESS;
 }
 
@@ -119,20 +215,40 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
   TRY(op->masked_dofmap.alloc(static_cast<size_t>(d->ncells * nd3 > 0 ? d->ncells * nd3 : 1)));
   TRY(build_masked_dofmap(d->ncells * nd3, op->cell_dofmap.ptr, op->bc_marker.ptr, op->masked_dofmap.ptr,
                           nullptr));
+  // Geometry variant.  On the fly needs the 1-D rule behind the caller's 3-D tables and a kernel for this nq.
+  {
+    std::vector<char> wbuf, dbuf;
+    TRY(copy_table(wbuf, d->weights, static_cast<size_t>(nq3) * ts));
+    TRY(copy_table(dbuf, d->dphi_geometry, static_cast<size_t>(3) * nq3 * 8 * ts));
+    if (d->scalar_bits == 64)
+      recover_1d_rule<double>(op, wbuf, dbuf);
+    else
+      recover_1d_rule<float>(op, wbuf, dbuf);
+  }
+  const bool want_otf = (d->flags & BD_FLAG_GEOMETRY_ONTHEFLY) != 0;
+  const bool want_pre = (d->flags & BD_FLAG_GEOMETRY_PRECOMPUTED) != 0;
+  if (want_otf && want_pre)
+    return guard_fail(fail(BD_ERR_INVALID_ARGUMENT, "both geometry flags set"));
+  const bool otf_possible = !op->w1d.empty() && otf_supported(op->degree, op->nq);
+  if (want_otf && !otf_possible)
+    return guard_fail(fail(BD_ERR_UNSUPPORTED,
+                           "on-the-fly geometry needs tensor-product quadrature weights, the trilinear coordinate "
+                           "element in tensor-product vertex order and nq <= 8 (nq = %d)", op->nq));
+  if (otf_possible && !want_pre)
+    TRY(d->scalar_bits == 64 ? count_nonaffine<double>(op) : count_nonaffine<float>(op));
+  // default: the shortcut kernel when every cell is a parallelepiped (no G stream at all), a stored G otherwise
+  // (measured: the general on-the-fly kernel roughly ties with streaming G in fp64)
+  if (want_otf)
+    op->geom_mode = op->n_nonaffine == 0 ? 1 : 2;
+  else if (!want_pre && otf_possible && op->n_nonaffine == 0)
+    op->geom_mode = 1;
+  else
+    op->geom_mode = 0;
   // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272), written
   // straight into the layout the stiffness kernel streams; lcells and bcells are separate segments
   // because they are separate launches (the bcells pointer offset of src/laplacian.hpp:329).
-  op->g_layout = preferred_g_layout(op->scalar_bits, op->degree, op->nq);
-  op->g_bcells_offset = g_layout_size(op->g_layout, op->nq, op->n_lcells);
-  const std::int64_t g_total = op->g_bcells_offset + g_layout_size(op->g_layout, op->nq, op->n_bcells);
-  TRY(op->G.alloc(static_cast<size_t>(g_total > 0 ? g_total : 1) * ts));
-  TRY(geometry_compute_layout(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
-                              op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, op->n_lcells,
-                              op->G.ptr, nullptr, op->g_layout));
-  TRY(geometry_compute_layout(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
-                              op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr + op->n_lcells,
-                              op->n_bcells, op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts, nullptr,
-                              op->g_layout));
+  if (op->geom_mode == 0)
+    TRY(precompute_geometry(op));
   if (cudaDeviceSynchronize() != cudaSuccess) // device_synchronize()  (src/laplacian.hpp:224)
     return guard_fail(fail(BD_ERR_CUDA, "geometry precompute failed: %s",
                            cudaGetErrorString(cudaGetLastError())));
@@ -164,7 +280,16 @@ extern "C" int bd_laplacian_geometry(bd_laplacian* op, const void** G_dev, int64
   const std::int64_t nlist = op->n_lcells + op->n_bcells;
   const size_t ts = op->scalar_size();
   const size_t bytes = static_cast<size_t>(nlist) * op->g_cell_stride() * ts;
-  if (op->G_reference.count != bytes || bytes == 0)
+  if (op->geom_mode != 0 && (op->G_reference.count != bytes || bytes == 0))
+  {
+    // on-the-fly operator: G exists only on request (tests, the assembled-CSR check), in the reference layout
+    BD_CHECK(op->G_reference.alloc(bytes > 0 ? bytes : 1));
+    BD_CHECK(geometry_compute_layout(op->scalar_bits, op->nq, op->xgeom.ptr, op->geometry_dofmap.ptr,
+                                     op->dphi_geometry.ptr, op->weights.ptr, op->cell_list.ptr, nlist,
+                                     op->G_reference.ptr, nullptr, 0));
+    BD_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+  }
+  else if (op->G_reference.count != bytes || bytes == 0)
   {
     BD_CHECK(op->G_reference.alloc(bytes > 0 ? bytes : 1));
     BD_CHECK(layout_g_to_reference(op->scalar_bits, op->nq, op->G.ptr, op->G_reference.ptr, op->n_lcells,
@@ -198,6 +323,11 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
   a.slab = true;
   a.g_layout = op->g_layout;
   a.mdofmap = op->masked_dofmap.ptr;
+  a.geom_mode = op->geom_mode;
+  a.xgeom = op->xgeom.ptr;
+  a.gdofmap = op->geometry_dofmap.ptr;
+  a.w1d = op->w1d.data();
+  a.pts1d = op->pts1d.data();
   if (part == 0)
   {
     // set_value(out, 0) over owned + ghost entries (src/laplacian.hpp:359)
@@ -242,7 +372,23 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
                        : op->g_layout == 0 ? "bd::stiffness_pencil_kernel (register pencils, streamed G rows)"
                        : (stiffness_variant() == 1 ? "bd::stiffness_slab_kernel (register slabs, LDG G)"
                                                    : "bd::stiffness_slab_tma_kernel (register slabs, UBLKCP G ring)");
+  if (op->geom_mode != 0)
+  {
+    kernel = op->nq >= 7 ? "bd::stiffness_mma8_otf_kernel (fp64 DMMA m8n8k4 arithmetic, geometry on the fly)"
+                         : "bd::stiffness_slab_otf_kernel (register slabs, geometry on the fly)";
+    snprintf(buf, n, "%s, T=%s, P=%d, nq=%d, %s", kernel, t, op->degree, op->nq,
+             op->geom_mode == 1 ? "all cells affine: G(q) = w_q G_cell" : "general cells: J(q) from the 8 vertices");
+    return BD_SUCCESS;
+  }
   snprintf(buf, n, "%s, T=%s, P=%d, nq=%d, G layout %d", kernel, t, op->degree, op->nq, op->g_layout);
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_laplacian_geometry_mode(bd_laplacian* op, int* mode, int64_t* n_nonaffine)
+{
+  BD_REQUIRE(op && mode && n_nonaffine, "bd_laplacian_geometry_mode: null argument");
+  *mode = op->geom_mode;
+  *n_nonaffine = op->n_nonaffine;
   return BD_SUCCESS;
 }
 

@@ -39,5 +39,10 @@ struct bd_laplacian
   int g_layout = 1; // 0 reference order (pencil kernel), 1 slab, 2 DMMA accumulator order (see stiffness_launch.cuh)
   std::int64_t g_bcells_offset = 0; // scalars before the bcells segment
   bd::DeviceArray<char> G_reference; // reference-layout copy, built on demand (bd_laplacian_geometry)
+  // Geometry variant (bd_laplacian_desc.flags): 0 = G precomputed and streamed, 1 = computed
+  // on the fly and every cell of both lists is affine (shortcut kernel), 2 = on the fly, general cells.
+  int geom_mode = 0;
+  std::int64_t n_nonaffine = -1;      // cells of [lcells, bcells] that are not parallelepipeds (-1: not counted)
+  std::vector<double> w1d, pts1d;     // 1-D rule recovered from weights / dphi_geometry (empty: not tensor-product)
   std::int64_t g_cell_stride() const { return 6ll * nq * nq * nq; }
 };

@@ -48,6 +48,15 @@ int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::i
   return BD_SUCCESS;
 }
 
+int otf_minb_variant()
+{
+  static const int v = [] {
+    const char* e = std::getenv("BD_OTF_MINB");
+    return e ? std::atoi(e) : 0;
+  }();
+  return v;
+}
+
 int preferred_g_layout(int scalar_bits, int degree, int nq)
 {
   // pencil kernel (reference layout): see pencil_instantiated() in stiffness_launch.cuh
@@ -70,6 +79,19 @@ std::int64_t g_layout_size(int layout, int nq, std::int64_t ncells)
 
 int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const StiffnessArgs& a)
 {
+  if (a.geom_mode != 0)
+  {
+    // geometry on the fly: slab kernel for nq <= 6, DMMA kernel for nq = 7, 8
+    if (scalar_bits != 32 && scalar_bits != 64)
+      return fail(BD_ERR_INVALID_ARGUMENT, "Invalid float size. Must be 32 or 64.");
+    if (!otf_supported(degree, nq) || identity != (nq == degree + 1))
+      return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry is not available for degree %d, nq %d", degree, nq);
+    if (nq >= 7)
+      return launch_stiffness_mma8_otf(scalar_bits, degree, identity, a);
+    if (identity)
+      return scalar_bits == 64 ? launch_stiffness_otf_f64_q0(degree, a) : launch_stiffness_otf_f32_q0(degree, a);
+    return scalar_bits == 64 ? launch_stiffness_otf_f64_q1(degree, a) : launch_stiffness_otf_f32_q1(degree, a);
+  }
   if (a.g_layout == 2)
   {
     if (nq != 8 && nq != 7)

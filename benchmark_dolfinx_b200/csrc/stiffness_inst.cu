@@ -8,8 +8,38 @@
 #define BD_CAT_(a, b, c) a##b##_q##c
 #define BD_CAT(a, b, c) BD_CAT_(a, b, c)
 
+#define BD_CAT_OTF_(a, b, c) a##b##_q##c
+#define BD_CAT_OTF(a, b, c) BD_CAT_OTF_(a, b, c)
+
 namespace bd
 {
+#ifdef BD_INST_OTF
+// ---- on-the-fly geometry (slab kernel, nq <= 6)
+#if BD_INST_QMODE == 0
+#define BD_OTF_CASE(P)                                                                             \
+  case P:                                                                                          \
+    return launch_stiffness_slab_otf<BD_INST_T, P, P + 1, true>(a);
+#else
+#define BD_OTF_CASE(P)                                                                             \
+  case P:                                                                                          \
+    return launch_stiffness_slab_otf<BD_INST_T, P, P + 2, false>(a);
+#endif
+int BD_CAT_OTF(launch_stiffness_otf_, BD_INST_SUFFIX, BD_INST_QMODE)(int degree, const StiffnessArgs& a)
+{
+  switch (degree)
+  {
+    BD_OTF_CASE(1)
+    BD_OTF_CASE(2)
+    BD_OTF_CASE(3)
+    BD_OTF_CASE(4)
+#if BD_INST_QMODE == 0
+    BD_OTF_CASE(5)
+#endif
+  default:
+    return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");
+  }
+}
+#else
 #if BD_INST_QMODE == 0
 #define BD_CASE(P)                                                                                 \
   case P:                                                                                          \
@@ -39,4 +69,5 @@ int BD_CAT(launch_stiffness_, BD_INST_SUFFIX, BD_INST_QMODE)(int degree, const S
     return fail(BD_ERR_UNSUPPORTED, "Unsupported degree [operator]");
   }
 }
+#endif // BD_INST_OTF
 } // namespace bd

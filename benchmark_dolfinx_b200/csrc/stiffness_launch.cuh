@@ -6,6 +6,7 @@
 #include "stiffness_slab.cuh"
 #include "stiffness_pencil.cuh"
 #include "stiffness_pencil_bulk.cuh"
+#include "stiffness_slab_otf.cuh"
 
 namespace bd
 {
@@ -29,6 +30,13 @@ struct StiffnessArgs
   const std::int32_t* mdofmap = nullptr; // dofmap with the BC marker in bit 31 (asynchronous-copy kernel)
   bool slab = false; // G is in the slab layout (stiffness_slab.cuh) and the slab kernel is used
   int g_layout = 0;  // 0 reference, 1 slab, 2 DMMA accumulator order
+  // geometry on the fly (stiffness_slab_otf.cuh, stiffness_mma8_otf.cuh): no G; 1 = every cell of the list is
+  // affine (verified by the caller), 2 = general cells (affine batches still take the shortcut)
+  int geom_mode = 0;
+  const void* xgeom = nullptr;           // T [nnodes][3]
+  const std::int32_t* gdofmap = nullptr; // [ncells][8], tensor-product vertex order
+  const double* w1d = nullptr;           // host, [nq] 1-D quadrature weights
+  const double* pts1d = nullptr;         // host, [nq] 1-D quadrature points
 };
 
 template <typename T, int P, int NQ, bool IDENTITY>
@@ -211,6 +219,88 @@ int launch_stiffness_slab(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
+// Slab kernel with on-the-fly geometry (stiffness_slab_otf.cuh), nq <= 6.
+int otf_minb_variant(); // TEMPORARY (A/B of the register cap): env BD_OTF_MINB
+
+template <typename T, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int MINB = 1>
+int launch_stiffness_slab_otf_cfg(const StiffnessArgs& a)
+{
+  using C = SlabConfig<T, P, NQ>;
+  constexpr int ND = P + 1;
+  constexpr int WARPS = 1;
+  // the gather prefetch needs 3 * nd^2 extra registers: affordable up to nd = 5 (as in the stored-G kernel)
+  constexpr bool PF = NQ <= 5 || (NQ == 6 && ND <= 5);
+  using OC = SlabOtfConfig<T, P, NQ, WARPS>;
+  static_assert(OC::SUPPORTED, "exchange cube exceeds shared memory");
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d || !a.pts1d)
+    return fail(BD_ERR_INVALID_ARGUMENT, "on-the-fly geometry needs the masked dofmap, vertices and 1-D rule");
+  auto kernel = stiffness_slab_otf_kernel<T, P, NQ, IDENTITY, AFFINE_ONLY, WARPS, PF, MINB>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OC::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, OC::THREADS, OC::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  SlabOtfTables<T, ND, NQ> tab;
+  fill_slab_tables<T, ND, NQ, IDENTITY>(tab.fwd, a.phi0_host, a.dphi1_host);
+  for (int q = 0; q < NQ; ++q)
+  {
+    tab.w[q] = static_cast<T>(a.w1d[q]);
+    tab.pts[q] = static_cast<T>(a.pts1d[q]);
+    for (int i = 0; i < ND; ++i)
+    {
+      // weights folded into the transposed contractions; with Phi = I they are applied per point instead
+      const double wq = IDENTITY ? 1.0 : a.w1d[q];
+      tab.bwd.phi[q * ND + i] = static_cast<T>(wq * static_cast<double>(tab.fwd.phi[q * ND + i]));
+      tab.bwd.dphi[q * ND + i] = static_cast<T>(wq * static_cast<double>(tab.fwd.dphi[q * ND + i]));
+    }
+  }
+  const std::int64_t nbatches = (a.ncells + C::CW - 1) / C::CW;
+  const std::int64_t want = (nbatches + WARPS - 1) / WARPS;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(clamp_grid(want, max_grid));
+  kernel<<<grid, OC::THREADS, OC::CTA_SMEM, a.stream>>>(
+      static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.xgeom), a.gdofmap,
+      static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+template <typename T, int P, int NQ, bool IDENTITY>
+int launch_stiffness_slab_otf(const StiffnessArgs& a)
+{
+  if constexpr (NQ > 6)
+    return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");
+  else
+  {
+    if constexpr (sizeof(T) == 8 && NQ == 5 && !IDENTITY)
+    {
+      const int mb = otf_minb_variant();
+      if (mb == 10)
+        return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 10>(a)
+                                : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 10>(a);
+      if (mb == 12)
+        return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 12>(a)
+                                : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 12>(a);
+      if (mb == 14)
+        return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 14>(a)
+                                : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 14>(a);
+    }
+    return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true>(a)
+                            : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false>(a);
+  }
+}
+
 // The pencil kernel (stiffness_pencil.cuh) is instantiated where it wins or is the only kernel without
 // spills (A/B in profiles/): qmode 1 with nq = 9, and fp32 with nq = 7, 8.
 template <typename T, int NQ, bool IDENTITY>
@@ -353,6 +443,15 @@ int launch_stiffness_f64_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_f64_q1(int degree, const StiffnessArgs& a);
 int launch_stiffness_f32_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_f32_q1(int degree, const StiffnessArgs& a);
+// on-the-fly geometry, nq <= 6 (same four units, compiled with -DBD_INST_OTF)
+int launch_stiffness_otf_f64_q0(int degree, const StiffnessArgs& a);
+int launch_stiffness_otf_f64_q1(int degree, const StiffnessArgs& a);
+int launch_stiffness_otf_f32_q0(int degree, const StiffnessArgs& a);
+int launch_stiffness_otf_f32_q1(int degree, const StiffnessArgs& a);
+// in stiffness_mma8.cu: on-the-fly geometry for nq = 7, 8
+int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const StiffnessArgs& a);
+// on-the-fly geometry exists for this (degree, nq)?
+inline bool otf_supported(int degree, int nq) { return nq >= 2 && nq <= 8 && (nq == degree + 1 || nq == degree + 2); }
 
 // in geometry.cu
 // G layouts: 0 = reference [cell][6][nq^3] (pencil kernel), 1 = slab (stiffness_slab.cuh), 2 = DMMA

@@ -1,6 +1,7 @@
 // Launcher of the fp64 tensor-core kernel (stiffness_mma8.cuh).
 #include "stiffness_launch.cuh"
 #include "stiffness_mma8.cuh"
+#include "stiffness_mma8_otf.cuh"
 
 
 namespace bd
@@ -67,5 +68,77 @@ int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const Stif
   BD_MMA8_CASE(6, 7, true)
 #undef BD_MMA8_CASE
   return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers nq = 7 and nq = 8 only");
+}
+
+template <typename TS, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int MINB = 1, bool PREFETCH = true>
+static int launch_mma8_otf(const StiffnessArgs& a)
+{
+  constexpr int ND = P + 1;
+  constexpr int kWarps = 4;
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d || !a.pts1d)
+    return fail(BD_ERR_INVALID_ARGUMENT, "on-the-fly geometry needs the masked dofmap, vertices and 1-D rule");
+  auto kernel = stiffness_mma8_otf_kernel<TS, P, NQ, IDENTITY, kWarps, AFFINE_ONLY, MINB, PREFETCH>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kWarps * 32, 0));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  Mma8OtfTables tab{};
+  const TS* phi = static_cast<const TS*>(a.phi0_host);   // [NQ][ND]
+  const TS* dphi = static_cast<const TS*>(a.dphi1_host); // [NQ][NQ]
+  for (int q = 0; q < 8; ++q)
+  {
+    tab.w[q] = q < NQ ? a.w1d[q] : 0.0;
+    tab.pts[q] = q < NQ ? a.pts1d[q] : 0.5;
+    for (int i = 0; i < 8; ++i)
+    {
+      tab.base.phi[q * 8 + i] = (q < NQ && i < ND) ? phi[q * ND + i] : 0.0;
+      tab.base.dphi[q * 8 + i] = (q < NQ && i < NQ) ? dphi[q * NQ + i] : 0.0;
+      tab.wphi[q * 8 + i] = tab.w[q] * tab.base.phi[q * 8 + i];
+    }
+  }
+  const std::int64_t want = (a.ncells + kWarps - 1) / kWarps;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(clamp_grid(want, max_grid));
+  kernel<<<grid, kWarps * 32, 0, a.stream>>>(
+      static_cast<const TS*>(a.u), static_cast<TS*>(a.y), static_cast<const TS*>(a.xgeom), a.gdofmap,
+      static_cast<const TS*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const StiffnessArgs& a)
+{
+#define BD_MMA8_OTF_CASE(P, NQ, ID)                                                                \
+  if (degree == P && identity == ID)                                                               \
+  {                                                                                                \
+    if (scalar_bits == 64 && otf_minb_variant() == 30)                                             \
+      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true, 3, false>(a)              \
+                              : launch_mma8_otf<double, P, NQ, ID, false, 3, false>(a);            \
+    if (scalar_bits == 64 && otf_minb_variant() == 3)                                              \
+      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true, 3>(a)                     \
+                              : launch_mma8_otf<double, P, NQ, ID, false, 3>(a);                   \
+    if (scalar_bits == 64)                                                                         \
+      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true>(a)                        \
+                              : launch_mma8_otf<double, P, NQ, ID, false>(a);                      \
+    return a.geom_mode == 1 ? launch_mma8_otf<float, P, NQ, ID, true>(a)                           \
+                            : launch_mma8_otf<float, P, NQ, ID, false>(a);                         \
+  }
+  BD_MMA8_OTF_CASE(6, 8, false)
+  BD_MMA8_OTF_CASE(7, 8, true)
+  BD_MMA8_OTF_CASE(5, 7, false)
+  BD_MMA8_OTF_CASE(6, 7, true)
+#undef BD_MMA8_OTF_CASE
+  return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the DMMA kernel covers nq = 7 and nq = 8 only");
 }
 } // namespace bd

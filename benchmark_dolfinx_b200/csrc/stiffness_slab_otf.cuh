@@ -16,8 +16,10 @@
 //     one of its cells is affine to within the rounding of the stored coordinates (decided in the kernel from the
 //     vertices it has loaded anyway); the AFFINE_ONLY instantiation is used when the operator has verified at
 //     construction that every cell of the mesh is.
-//   * The quadrature weight w_q0 w_q1 w_q2 is folded into the tables of the transposed contractions
-//     (rows of Phi / DPhi scaled by the 1-D weight), kappa into G_cell resp. 1/det J.
+//   * Quadrature weights: w_q1 w_q2 are folded into the tables of the transposed y/z contractions (rows of Phi /
+//     DPhi scaled by the 1-D weight), w_q0 is applied per point (a second, weighted pair of tables in the middle
+//     phase costs ~80 registers: with no constant-bank operand for DFMA the compiler keeps the entries of a
+//     rolled loop in registers); kappa goes into G_cell resp. 1/det J.
 //
 // Everything else (teams of NQ lanes, register slabs, exchange cube, masked dofmap, prefetch of the next batch's
 // dof indices and values) is the slab kernel of stiffness_slab.cuh; there is no ring and no mbarrier.
@@ -71,9 +73,11 @@ struct TrilinearMap
     }
     scale = s;
   }
-  __device__ __forceinline__ bool affine() const
+  __device__ __forceinline__ bool affine() const { return affine(otf_affine_eps<T>()); }
+  // `eps`: relative rounding level of the *stored* coordinates (they may be float while T is double)
+  __device__ __forceinline__ bool affine(T eps) const
   {
-    const T tol = otf_affine_eps<T>() * scale;
+    const T tol = eps * scale;
     T m = 0;
 #pragma unroll
     for (int i = 0; i < 3; ++i)
@@ -138,7 +142,7 @@ __device__ __forceinline__ void otf_apply_kkt(const T (&K)[3][3], T s, T gx, T g
 // Z phase of lane (c, q2) for one q1: x contractions, G from the cell geometry, transposed x contractions.
 // AFFINE: G = (w) Gc.  Otherwise J(q) from the hoisted column pieces:
 //   col0 (constant along q0), col1 = B0 + A1 xi0, col2 = C0 + C1 xi0.
-// `wrow` = w_q1 w_q2 when the weights are applied here (IDENTITY), unused otherwise.
+// `wrow` = w_q1 w_q2 when those weights are applied here (IDENTITY: no transposed interpolation to carry them).
 template <typename T, int ND, int NQ, bool IDENTITY, bool AFFINE>
 __device__ __forceinline__ void slab_z_points_otf(const SlabOtfTables<T, ND, NQ>& tab, const T (&ax)[ND],
                                                   const T (&ay)[ND], const T (&az)[ND], T (&bx)[ND], T (&by)[ND],
@@ -177,13 +181,10 @@ __device__ __forceinline__ void slab_z_points_otf(const SlabOtfTables<T, ND, NQ>
       fx = Gc[0] * gx + Gc[1] * gy + Gc[2] * gz;
       fy = Gc[1] * gx + Gc[3] * gy + Gc[4] * gz;
       fz = Gc[2] * gx + Gc[4] * gy + Gc[5] * gz;
-      if constexpr (IDENTITY)
-      {
-        const T wq = wrow * tab.w[q0];
-        fx *= wq;
-        fy *= wq;
-        fz *= wq;
-      }
+      const T wq = IDENTITY ? wrow * tab.w[q0] : tab.w[q0];
+      fx *= wq;
+      fy *= wq;
+      fz *= wq;
     }
     else
     {
@@ -197,9 +198,7 @@ __device__ __forceinline__ void slab_z_points_otf(const SlabOtfTables<T, ND, NQ>
       }
       T K[3][3], det;
       otf_adjugate(col0, col1, col2, K, det);
-      T s = kappa * otf_rcp(det);
-      if constexpr (IDENTITY)
-        s *= wrow * tab.w[q0];
+      const T s = kappa * otf_rcp(det) * (IDENTITY ? wrow * tab.w[q0] : tab.w[q0]);
       otf_apply_kkt(K, s, gx, gy, gz, fx, fy, fz);
     }
     if constexpr (IDENTITY)
@@ -208,20 +207,34 @@ __device__ __forceinline__ void slab_z_points_otf(const SlabOtfTables<T, ND, NQ>
       bz[q0] = fz;
 #pragma unroll
       for (int i = 0; i < ND; ++i)
-        bx[i] += tab.bwd.dphi[q0 * ND + i] * fx;
+        bx[i] += tab.fwd.dphi[q0 * ND + i] * fx;
     }
     else
     {
 #pragma unroll
       for (int i = 0; i < ND; ++i)
       {
-        bx[i] += tab.bwd.dphi[q0 * ND + i] * fx;
-        by[i] += tab.bwd.phi[q0 * ND + i] * fy;
-        bz[i] += tab.bwd.phi[q0 * ND + i] * fz;
+        bx[i] += tab.fwd.dphi[q0 * ND + i] * fx;
+        by[i] += tab.fwd.phi[q0 * ND + i] * fy;
+        bz[i] += tab.fwd.phi[q0 * ND + i] * fz;
       }
     }
   }
 }
+
+// Scheduling fence.  The stored-G kernels wait on an mbarrier in every y-tile / G slot, and ptxas does not move
+// instructions across that spin loop: the unrolled tiles stay in program order and the DMMA kernel needs 164
+// registers.  Take the wait away (nothing to wait for here) and the tiles become one basic block that ptxas
+// interleaves until 255 registers and 400+ bytes of spills; neither __syncwarp, nor an empty asm with a memory
+// clobber, nor a branch on a register brings the order back (tried, compile-only).  So the on-the-fly kernels keep one
+// mbarrier per warp whose first phase is completed once at start-up; waiting for that phase returns at once.
+__device__ __forceinline__ void sched_fence_init(std::uint64_t* bar)
+{
+  mbar_init(bar, 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void sched_fence(std::uint64_t* bar) { mbar_wait(bar, 0); }
 
 template <typename T, int P, int NQ, int WARPS_>
 struct SlabOtfConfig
@@ -230,12 +243,12 @@ struct SlabOtfConfig
   static constexpr int CUBE_BYTES = (3 * Base::CUBE * int(sizeof(T)) + 15) / 16 * 16;
   static constexpr int WARPS = WARPS_;
   static constexpr int THREADS = WARPS * 32;
-  static constexpr int CTA_SMEM = WARPS * CUBE_BYTES;
+  static constexpr int CTA_SMEM = WARPS * CUBE_BYTES + WARPS * 8; // + one mbarrier per warp (sched_fence)
   static constexpr bool SUPPORTED = CTA_SMEM <= 226 * 1024;
 };
 
-template <typename T, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int WARPS_, bool PREFETCH>
-__global__ void __launch_bounds__(WARPS_ * 32)
+template <typename T, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int WARPS_, bool PREFETCH, int MINB = 1>
+__global__ void __launch_bounds__(WARPS_ * 32, MINB)
     stiffness_slab_otf_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ xgeom,
                               const std::int32_t* __restrict__ gdofmap, const T* __restrict__ cell_constants,
                               const std::int32_t* __restrict__ mdofmap, const std::int32_t* __restrict__ cells,
@@ -254,6 +267,10 @@ __global__ void __launch_bounds__(WARPS_ * 32)
   const bool lane_ok = c < CW;
   T* cube = reinterpret_cast<T*>(smem_raw + warp * OC::CUBE_BYTES);
   const int rbase = (lane_ok ? c : 0) * NQ;
+  std::uint64_t* fbar = reinterpret_cast<std::uint64_t*>(smem_raw + OC::WARPS * OC::CUBE_BYTES) + warp;
+  if (lane == 0)
+    sched_fence_init(fbar);
+  __syncwarp();
 
   const int nbatches = (ncells + CW - 1) / CW;
   const int warps_total = gridDim.x * OC::WARPS;
@@ -456,6 +473,7 @@ __global__ void __launch_bounds__(WARPS_ * 32)
         by[i] = 0;
         bz[i] = 0;
       }
+      sched_fence(fbar);
       const T wrow = IDENTITY ? tab.w[q1] * w2 : T(1);
       if (zactive)
       {

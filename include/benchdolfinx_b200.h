@@ -84,6 +84,14 @@ typedef struct bd_laplacian_desc
 } bd_laplacian_desc;
 
 #define BD_FLAG_BORROW_DEVICE_ARRAYS 1u
+/* Geometry variant of the operator (reference: geometry_computation_gpu fills G once, src/laplacian.hpp:238-272,
+ * and stiffness_operator_gpu streams it, src/laplacian_gpu.hpp:256-273).  Default (neither flag): G is computed on
+ * the fly inside the stiffness kernel when every cell of the mesh is a parallelepiped (G(q) = w_q G_cell, no G
+ * array at all), precomputed and streamed otherwise.  The flags force one or the other; on-the-fly needs the
+ * tensor-product quadrature / trilinear coordinate element the reference uses and nq <= 8, else
+ * BD_ERR_UNSUPPORTED. */
+#define BD_FLAG_GEOMETRY_ONTHEFLY 2u
+#define BD_FLAG_GEOMETRY_PRECOMPUTED 4u
 
 /* Constructor: copies/borrows the arrays, precomputes G over [lcells..., bcells...]
  * (compute_geometry, src/laplacian.hpp:214-224,238-272) on the current device. */
@@ -123,6 +131,10 @@ int bd_laplacian_apply_host_batch(bd_laplacian* op, struct bd_halo* halo, int nv
  * and the number of launches since the last read, and resets the counters.  (The reference only
  * has dolfinx::common::Timer scopes around whole phases, src/laplacian_solver.cpp:90,197.) */
 int bd_laplacian_profile(bd_laplacian* op, int enable);
+/* Which geometry variant the operator uses (no counterpart in the reference, which always precomputes):
+ * *mode = 0 precomputed G, 1 on the fly with every cell affine, 2 on the fly with general cells;
+ * *n_nonaffine = number of listed cells that are not parallelepipeds (to the rounding of their coordinates). */
+int bd_laplacian_geometry_mode(bd_laplacian* op, int* mode, int64_t* n_nonaffine);
 /* One-line description of the stiffness kernel variant this operator launches (for reports). */
 int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n);
 int bd_laplacian_profile_read(bd_laplacian* op, double* total_ms, int64_t* launches);

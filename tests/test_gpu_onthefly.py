@@ -1,0 +1,145 @@
+"""Geometry on the fly (csrc/stiffness_slab_otf.cuh, csrc/stiffness_mma8_otf.cuh) against the oracle.
+
+The reference always precomputes G (geometry_computation_gpu, src/geometry_gpu.hpp:89-130) and streams it
+(src/laplacian_gpu.hpp:256-273).  The on-the-fly variants rebuild it in the stiffness kernel from the cell
+vertices: the general trilinear path and the shortcut for parallelepipeds (G(q) = w_q G_cell).  Same oracle, same
+tolerances as every other operator test; grids capped so that each warp also runs its steady state.
+"""
+import numpy as np
+import pytest
+
+from oracle.boxmesh import compute_mesh_size, create_box_mesh
+from oracle.laplacian import OracleLaplacian
+from oracle.tables import Tables as OracleTables
+
+pytestmark = pytest.mark.gpu
+
+RTOL = {np.float64: 1e-12, np.float32: 1e-5}
+
+
+def _rel(a, b):
+    return np.linalg.norm(a.astype(np.float64) - b.astype(np.float64)) / np.linalg.norm(b.astype(np.float64))
+
+
+class _Mesh:
+    """Oracle mesh with replaced vertex coordinates."""
+
+    def __init__(self, mesh, xgeom):
+        for k in ("cell_dofmap", "geometry_dofmap", "bc_marker", "lcells", "bcells", "ndofs_local", "ncells"):
+            setattr(self, k, getattr(mesh, k))
+        self.ndofs_owned = mesh.ndofs_local
+        self.xgeom = xgeom
+
+
+def _case(degree, qmode, kind):
+    """kind: box (axis-aligned), sheared (affine map of the box: parallelepipeds), perturbed (general hexahedra),
+    mixed (a few perturbed vertices in an otherwise sheared mesh)."""
+    mesh = create_box_mesh(compute_mesh_size(12000, degree), degree,
+                           geom_perturb_fact=0.2 if kind == "perturbed" else 0.0)
+    x = mesh.xgeom.copy()
+    if kind in ("sheared", "mixed"):
+        A = np.array([[1.0, 0.3, -0.2], [0.1, 0.9, 0.25], [-0.15, 0.2, 1.1]])
+        x = x @ A.T + np.array([0.3, -0.1, 0.2])
+    if kind == "mixed":
+        rng = np.random.default_rng(7)
+        h = 1.0 / max(compute_mesh_size(12000, degree))
+        pick = rng.choice(len(x), size=max(1, len(x) // 15), replace=False)
+        x[pick] += rng.uniform(-0.15 * h, 0.15 * h, (len(pick), 3))
+    m = _Mesh(mesh, x)
+    oracle = OracleLaplacian(m, OracleTables(degree, qmode), kappa=2.0, dtype=np.float64)
+    u = np.random.default_rng(10 * degree + qmode).uniform(-1, 1, mesh.ndofs_local)
+    return m, u, oracle
+
+
+_CACHE = {}
+
+
+def _cached(degree, qmode, kind):
+    key = (degree, qmode, kind)
+    if key not in _CACHE:
+        m, u, oracle = _case(degree, qmode, kind)
+        _CACHE[key] = (m, u, oracle.apply(u.copy()), oracle.G)
+    return _CACHE[key]
+
+
+@pytest.fixture
+def grid_cap():
+    import benchmark_dolfinx_b200 as bd
+    yield bd.debug_set_max_grid
+    bd.debug_set_max_grid(0)
+
+
+_PQ = [(p, q) for p in range(1, 8) for q in (0, 1) if p + 1 + q <= 8]
+
+
+@pytest.mark.parametrize("kind", ["box", "sheared", "perturbed", "mixed"])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("degree,qmode", _PQ)
+def test_onthefly_matches_oracle(degree, qmode, dtype, kind, grid_cap):
+    import torch
+    import benchmark_dolfinx_b200 as bd
+    m, u, y_ref, G_ref = _cached(degree, qmode, kind)
+    op = bd.MatFreeLaplacianGPU(m, degree, qmode, 2.0, dtype=dtype, geometry="onthefly")
+    mode, nonaffine = op.geometry_mode()
+    if kind in ("box", "sheared") and dtype == np.float64:
+        assert (mode, nonaffine) == ("onthefly-affine", 0)
+    if kind in ("perturbed", "mixed"):
+        assert mode == "onthefly-general" and nonaffine > 0
+    assert "on the fly" in op.describe()
+    ud = torch.from_numpy(u.astype(dtype)).cuda()
+    for cap in (2, 0):
+        grid_cap(cap)
+        for _ in range(2):
+            yd = torch.full_like(ud, 7.0)
+            op.apply(ud, yd)
+            torch.cuda.synchronize()
+            assert _rel(yd.cpu().numpy(), y_ref) < RTOL[dtype]
+    # G is not stored; on request it is computed in the reference's layout
+    assert _rel(op.geometry(), G_ref) < RTOL[dtype]
+
+
+def test_default_choice_and_forced_modes():
+    import torch
+    import benchmark_dolfinx_b200 as bd
+    for kind, expect in (("box", "onthefly-affine"), ("sheared", "onthefly-affine"), ("perturbed", "precomputed")):
+        m, u, y_ref, _ = _cached(3, 1, kind)
+        op = bd.MatFreeLaplacianGPU(m, 3, 1, 2.0)
+        assert op.geometry_mode()[0] == expect
+        pre = bd.MatFreeLaplacianGPU(m, 3, 1, 2.0, geometry="precomputed")
+        assert pre.geometry_mode()[0] == "precomputed"
+        ud = torch.from_numpy(u).cuda()
+        y1, y2 = torch.zeros_like(ud), torch.zeros_like(ud)
+        op.apply(ud, y1)
+        pre.apply(ud, y2)
+        torch.cuda.synchronize()
+        assert _rel(y1.cpu().numpy(), y_ref) < 1e-12 and _rel(y2.cpu().numpy(), y_ref) < 1e-12
+    # nq = 9 has no on-the-fly kernel: forcing it is an error, the default falls back to a stored G
+    m7 = create_box_mesh(compute_mesh_size(3000, 7), 7)
+    with pytest.raises(bd.BenchDolfinxError):
+        bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0, geometry="onthefly")
+    assert bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0).geometry_mode()[0] == "precomputed"
+
+
+def test_onthefly_cg_and_csr_check():
+    """CG through the on-the-fly operator equals the oracle's CG; the assembled-CSR check still works (G on demand)."""
+    import torch
+    import benchmark_dolfinx_b200 as bd
+    from oracle.laplacian import cg_solve
+    m, u, _, _ = _cached(3, 1, "sheared")
+    oracle = OracleLaplacian(m, OracleTables(3, 1), kappa=2.0, dtype=np.float64)
+    op = bd.MatFreeLaplacianGPU(m, 3, 1, 2.0)
+    assert op.geometry_mode()[0] == "onthefly-affine"
+    b = u.copy()
+    b[m.bc_marker != 0] = 0
+    x_ref = np.zeros_like(b)
+    its_ref = cg_solve(oracle.apply, x_ref, b, 8)
+    bd_, x = torch.from_numpy(b).cuda(), torch.zeros(len(b), dtype=torch.float64, device="cuda")
+    its = bd.cg_solve(op, x, bd_, 8)
+    torch.cuda.synchronize()
+    assert its == its_ref and _rel(x.cpu().numpy(), x_ref) < 1e-12
+    A = bd.MatrixOperator(op)
+    y, z = torch.zeros_like(bd_), torch.zeros_like(bd_)
+    op.apply(bd_, y)
+    A.apply(bd_, z)
+    torch.cuda.synchronize()
+    assert _rel(y.cpu().numpy(), z.cpu().numpy()) < 1e-12
