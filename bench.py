@@ -504,12 +504,12 @@ def e2e_leg(ctx, mesh, op, u, steps, tsize):
             if ctx.world == 1 else None}
 
 
-def build_case(ctx, bd, degree, qmode, dtype, ndofs_per_rank, ndofs_global, geometry):
+def build_case(ctx, bd, degree, qmode, dtype, ndofs_per_rank, ndofs_global, geometry, perturb=0.0):
     """Mesh, halo plan, operator and input vector of one configuration (global box as src/main.cpp:237-240,272-273)."""
     torch = ctx.torch
     n = bd.compute_mesh_size(ndofs_global or ndofs_per_rank * ctx.world, degree)
     t0 = time.perf_counter()
-    mesh = bd.BoxMesh(n, degree, ctx.rank, ctx.world, dtype=dtype)
+    mesh = bd.BoxMesh(n, degree, ctx.rank, ctx.world, geom_perturb_fact=perturb, dtype=dtype)
     halo = bd.Halo(ctx.comm, mesh) if ctx.world > 1 else None
     op = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, halo=halo, geometry=geometry)
     u = mesh.assemble_rhs(qmode)
@@ -537,6 +537,9 @@ def main():
                          "rebuilt on the fly in the stiffness kernel, or auto = the operator's own choice (on the fly "
                          "when every cell is a parallelepiped).  The other variant is measured too and reported "
                          "under `variants`")
+    ap.add_argument("--geom_perturb_fact", type=float, default=0.0,
+                    help="random perturbation of the mesh vertices as a fraction of the cell size (reference option "
+                         "of the same name, src/main.cpp:163); 0 = the benchmark's unperturbed box")
     ap.add_argument("--no-cg", action="store_true", help="skip the CG legs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
@@ -587,7 +590,7 @@ def main():
 
     # ---- headline legs: operator action, CG, end to end
     n, mesh, halo, op, u, y, t_setup = build_case(ctx, bd, degree, qmode, dtype, args.ndofs, args.ndofs_global,
-                                                  args.geometry)
+                                                  args.geometry, args.geom_perturb_fact)
     ndofs_global = mesh.ndofs_global
     head = action_leg(ctx, bd, mesh, op, u, y, args.steps, args.warmup, degree, qmode, args.float,
                       sample_clocks=True, local_rank=local_rank)
@@ -625,7 +628,7 @@ def main():
     if qmode != 0 and world == 1 and not args.no_cpu:
         del mesh, halo, u, y
         _, mesh0, halo0, op0, u0, y0, _ = build_case(ctx, bd, degree, 0, dtype, args.ndofs, args.ndofs_global,
-                                                     args.geometry)
+                                                     args.geometry, args.geom_perturb_fact)
         leg = action_leg(ctx, bd, mesh0, op0, u0, y0, max(3, args.steps // 2), args.warmup, degree, 0, args.float)
         gpu_q0 = {"value": leg["value"], "unit": "GDoF/s", "ms_per_step": leg["ms_per_step"],
                   "roofline_frac": leg["roofline"]["frac"], "geometry": leg["geometry"], "kernel": leg["roofline"]["kernel"],
@@ -684,6 +687,7 @@ def main():
     if rank == 0:
         cfg = dict(workload_config(args, world), ndofs_global_requested=args.ndofs_global or None, mesh_cells=n,
                    ndofs_global=ndofs_global, setup_seconds=t_setup, geometry=head_mode,
+                   geom_perturb_fact=args.geom_perturb_fact,
                    geometry_requested=args.geometry)
         line = {
             "metric": "gdof_per_second_laplacian_action", "value": head["value"], "unit": "GDoF/s",

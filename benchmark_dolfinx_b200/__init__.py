@@ -35,7 +35,7 @@ from ._lib import BenchDolfinxError, check, lib
 __all__ = [
     "BenchDolfinxError", "Tables", "BoxMesh", "Comm", "Halo", "MatFreeLaplacianGPU", "MatrixOperator",
     "cg_solve",
-    "axpy", "inner_product", "norm", "set_value", "compute_mesh_size", "partition_grid",
+    "axpy", "inner_product", "norm", "set_value", "pointwise_mult", "compute_mesh_size", "partition_grid",
     "laplace_action_gpu", "BenchmarkResults", "device_information",
 ]
 
@@ -402,6 +402,16 @@ class MatFreeLaplacianGPU:
         check(lib.bd_laplacian_geometry_mode(self._h, C.byref(mode), C.byref(n)))
         return ("precomputed", "onthefly-affine", "onthefly-general")[mode.value], n.value
 
+    def get_diag_inverse(self, diag_inv=None, stream=None):
+        """1 / diag(A) as a device vector (MatrixOperator::get_diag_inverse, src/csr.hpp:154-162, computed
+        matrix-free here; 1 on constrained rows).  Ghost entries are partial sums: use the owned part only."""
+        import torch
+        if diag_inv is None:
+            diag_inv = torch.empty(self.ndofs, dtype=_torch_dtype(self.bits), device="cuda")
+        self._check_vec(diag_inv)
+        check(lib.bd_laplacian_diagonal_inverse(self._h, diag_inv.data_ptr(), _stream_ptr(stream)))
+        return diag_inv
+
     def describe(self) -> str:
         buf = C.create_string_buffer(256)
         check(lib.bd_laplacian_describe(self._h, buf, 256))
@@ -484,8 +494,14 @@ def norm(a, n=None, comm: Comm | None = None) -> float:
     return math.sqrt(inner_product(a, a, n, comm))
 
 
+def pointwise_mult(w, x, y, n=None, stream=None):
+    """w = x * y over the first n (owned) entries (src/vector.hpp:266-285)."""
+    n = w.numel() if n is None else n
+    check(lib.bd_pointwise_mult(_bits(w.dtype), n, x.data_ptr(), y.data_ptr(), w.data_ptr(), _stream_ptr(stream)))
+
+
 def cg_solve(A: MatFreeLaplacianGPU, x, b, max_iter: int, rtol: float = 0.0, comm: Comm | None = None,
-             stream=None) -> int:
+             stream=None, diag_inv=None) -> int:
     """Unpreconditioned CG (src/cg.hpp:89-169); returns the iteration count.  For the matrix-free
     operator the whole solve is the fused device loop of bd_cg_solve; any other duck-typed operator
     (the CSR check operator) runs the same recurrence through the vector functions."""
@@ -494,9 +510,17 @@ def cg_solve(A: MatFreeLaplacianGPU, x, b, max_iter: int, rtol: float = 0.0, com
     if comm is None and getattr(A, "halo", None) is not None:
         comm = A.halo.comm            # the sums must run over the ranks the halo plan spans
     if not isinstance(A, MatFreeLaplacianGPU):
+        if diag_inv is not None:
+            raise BenchDolfinxError(-1, "Jacobi preconditioning is implemented for the matrix-free operator")
         return _cg_solve_generic(A, x, b, max_iter, rtol, comm)
     its = C.c_int(0)
     halo = A.halo._h if A.halo is not None else None
+    if diag_inv is not None:     # Jacobi: "p <- beta*p + M^-1(r)" (src/cg.hpp:165)
+        A._check_vec(diag_inv)
+        check(lib.bd_cg_solve_jacobi(A._h, halo, comm._h if comm is not None else None, x.data_ptr(), b.data_ptr(),
+                                     diag_inv.data_ptr(), int(max_iter), float(rtol), C.byref(its),
+                                     _stream_ptr(stream)))
+        return its.value
     check(lib.bd_cg_solve(A._h, halo, comm._h if comm is not None else None, x.data_ptr(), b.data_ptr(),
                           int(max_iter), float(rtol), C.byref(its), _stream_ptr(stream)))
     return its.value

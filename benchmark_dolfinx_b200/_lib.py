@@ -106,6 +106,9 @@ PROTOTYPES = {
     "bd_halo_end": (C.c_int, [_V, _V]),
     "bd_laplacian_apply_halo": (C.c_int, [_V, _V, _V, _V, _V]),
     "bd_cg_solve": (C.c_int, [_V, _V, _V, _V, _V, C.c_int, C.c_double, C.POINTER(C.c_int), _V]),
+    "bd_laplacian_diagonal_inverse": (C.c_int, [_V, _V, _V]),
+    "bd_pointwise_mult": (C.c_int, [C.c_int, C.c_int64, _V, _V, _V, _V]),
+    "bd_cg_solve_jacobi": (C.c_int, [_V, _V, _V, _V, _V, _V, C.c_int, C.c_double, C.POINTER(C.c_int), _V]),
     "bd_inner_product": (C.c_int, [_V, C.c_int, C.c_int64, _V, _V, C.POINTER(C.c_double)]),
     "bd_norm": (C.c_int, [_V, C.c_int, C.c_int64, _V, C.POINTER(C.c_double)]),
     "bd_csr_assemble": (C.c_int, [_V, C.c_int64, C.POINTER(_V)]),

@@ -283,19 +283,10 @@ int launch_stiffness_slab_otf(const StiffnessArgs& a)
     return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");
   else
   {
-    if constexpr (sizeof(T) == 8 && NQ == 5 && !IDENTITY)
-    {
-      const int mb = otf_minb_variant();
-      if (mb == 10)
-        return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 10>(a)
-                                : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 10>(a);
-      if (mb == 12)
-        return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 12>(a)
-                                : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 12>(a);
-      if (mb == 14)
-        return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 14>(a)
-                                : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 14>(a);
-    }
+    // TEMPORARY A/B: BD_OTF_MINB=12 caps the kernel at 168 registers (12 one-warp CTAs per SM)
+    if (otf_minb_variant() == 12)
+      return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 12>(a)
+                              : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 12>(a);
     return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true>(a)
                             : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false>(a);
   }

@@ -104,7 +104,6 @@ static int launch_mma8_otf(const StiffnessArgs& a)
     {
       tab.base.phi[q * 8 + i] = (q < NQ && i < ND) ? phi[q * ND + i] : 0.0;
       tab.base.dphi[q * 8 + i] = (q < NQ && i < NQ) ? dphi[q * NQ + i] : 0.0;
-      tab.wphi[q * 8 + i] = tab.w[q] * tab.base.phi[q * 8 + i];
     }
   }
   const std::int64_t want = (a.ncells + kWarps - 1) / kWarps;

@@ -7,9 +7,11 @@
 //   * general cell: the trilinear map's coefficients are reduced per y-tile (xi1 is the same for the whole warp in
 //     a tile) by lanes 0..7 into a small per-warp table in shared memory; a point then costs 6 FMA for J plus
 //     adj(J), det J and f = K (K^T g) w / det J.
-// Quadrature weights: with an interpolation matrix (qmode 1) they are folded into the three transposed
-// interpolations (rows of Phi scaled by the 1-D weight, no per-point work); with Phi = I they are applied per point
-// (w[q0] w[q2] per lane, w[q1] per tile).  Padded points of the nq = 7 case have weight 0.  Geometry arithmetic is fp64 also when vectors and coordinates are stored as float.
+// Quadrature weights are applied per point (w[q0] w[q2] per lane, w[q1] per tile): this kernel runs the
+// reference's chain interpolate -> gradient -> G -> gradient^T -> interpolate^T, and the transposed gradient mixes
+// the point index before the transposed interpolation sees it, so the weights cannot ride on a table as they do
+// in the re-associated slab kernel.  Padded points of the nq = 7 case have weight 0.  Geometry arithmetic is fp64
+// also when vectors and coordinates are stored as float.
 #pragma once
 
 #include "stiffness_mma8.cuh"
@@ -20,7 +22,6 @@ namespace bd
 struct Mma8OtfTables
 {
   Mma8Tables base;
-  double wphi[64]; // w[q] Phi[q][i]: the transposed interpolation carries the quadrature weights (Phi != I)
   double w[8];     // 1-D weights, 0 beyond nq
   double pts[8];   // 1-D points, 0.5 beyond nq
 };
@@ -34,7 +35,7 @@ constexpr int kMma8OtfWarpDoubles = 8 + 8 * 10;
 __device__ __forceinline__ double2 lds_f64x2(const double* p)
 {
   double2 v;
-  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(smem_addr(p)));
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(smem_addr(p)) : "memory");
   return v;
 }
 
@@ -69,19 +70,18 @@ __global__ void __launch_bounds__(kMma8Warps * 32, MINB)
   for (int s = 0; s < 2; ++s)
   {
     phi_col[s] = tab.phi[g * 8 + 2 * t + s];
-    phiT_col[s] = otab.wphi[(2 * t + s) * 8 + g];
+    phiT_col[s] = tab.phi[(2 * t + s) * 8 + g];
     d_col[s] = tab.dphi[g * 8 + 2 * t + s];
     dT_col[s] = tab.dphi[(2 * t + s) * 8 + g];
     phi_row[s] = tab.phi[g * 8 + 4 * s + t];
-    phiT_row[s] = otab.wphi[(4 * s + t) * 8 + g];
+    phiT_row[s] = tab.phi[(4 * s + t) * 8 + g];
     d_row[s] = tab.dphi[g * 8 + 4 * s + t];
     dT_row[s] = tab.dphi[(4 * s + t) * 8 + g];
   }
   const int src0 = 4 * t + (g >> 1), src1 = 4 * (4 + t) + (g >> 1);
   const bool odd = g & 1;
   // lane (g, t) owns the points (q0 = g, q1 = tile, q2 = 2t + s)
-  // weights applied per point only when there is no transposed interpolation to carry them
-  const double wl[2] = {IDENTITY ? otab.w[g] * otab.w[2 * t] : 1.0, IDENTITY ? otab.w[g] * otab.w[2 * t + 1] : 1.0};
+  const double wl[2] = {otab.w[g] * otab.w[2 * t], otab.w[g] * otab.w[2 * t + 1]};
   [[maybe_unused]] const double xi0 = otab.pts[g];
   [[maybe_unused]] const double xi2[2] = {otab.pts[2 * t], otab.pts[2 * t + 1]};
 
@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32, MINB)
       mma8_row(gx0, gx1, T[yy][0], T[yy][1], d_row, src0, src1, odd);
       mma8_col(gz0, gz1, T[yy][0], T[yy][1], d_col);
       double fx[2], fz[2];
-      const double wy = IDENTITY ? otab.w[yy] : 1.0;
+      const double wy = otab.w[yy];
       if (AFFINE_ONLY || affine)
       {
         const double2 g01 = lds_f64x2(gcs), g23 = lds_f64x2(gcs + 2), g45 = lds_f64x2(gcs + 4);
@@ -295,14 +295,10 @@ __global__ void __launch_bounds__(kMma8Warps * 32, MINB)
           double f0 = g01.x * gx + g01.y * gy + g23.x * gz;
           double f1 = g01.y * gx + g23.y * gy + g45.x * gz;
           double f2 = g23.x * gx + g45.x * gy + g45.y * gz;
-          if constexpr (IDENTITY)
-          {
-            const double wq = wl[s] * wy;
-            f0 *= wq, f1 *= wq, f2 *= wq;
-          }
-          fx[s] = f0;
-          F[yy][s] = f1;
-          fz[s] = f2;
+          const double wq = wl[s] * wy;
+          fx[s] = f0 * wq;
+          F[yy][s] = f1 * wq;
+          fz[s] = f2 * wq;
         }
       }
       else
@@ -352,7 +348,7 @@ __global__ void __launch_bounds__(kMma8Warps * 32, MINB)
 #pragma unroll
       for (int yy = 0; yy < 8; ++yy)
         mma8_col(W[yy][0], W[yy][1], R[yy][0], R[yy][1], phiT_col); // z
-      mma8_tile<true, false>(otab.wphi, W, R);                     // y (weighted rows)
+      mma8_tile<true, false>(tab.phi, W, R);                       // y
 #pragma unroll
       for (int yy = 0; yy < 8; ++yy)
       {

@@ -258,6 +258,23 @@ int bd_laplacian_apply_halo(bd_laplacian* op, bd_halo* halo, void* in_dev, void*
 int bd_cg_solve(bd_laplacian* op, bd_halo* halo, bd_comm* comm, void* x_dev, const void* b_dev,
                 int max_iter, double rtol, int* iterations, void* stream);
 
+/* Jacobi preconditioning.  The reference carries the scaffolding only: the inverse diagonal of the
+ * *assembled* matrix (compute_diag_inv, src/csr.hpp:79-107; MatrixOperator::get_diag_inverse, :154-162),
+ * pointwise_mult (src/vector.hpp:266-285) and the remark "p <- beta*p + M^-1(r)" in cg_solve
+ * (src/cg.hpp:165).
+ * bd_laplacian_diagonal_inverse: diag_inv_dev[i] = 1 / A_ii for the operator's ndofs entries, computed
+ * matrix-free from the operator's tables and geometry (1 on constrained rows, as the assembled matrix after
+ * set_diagonal, src/laplacian_solver.cpp:182-184).  Owned entries are complete; ghost entries hold partial
+ * sums and must not be used.  Synchronous (allocates and frees a temporary of ndofs doubles). */
+int bd_laplacian_diagonal_inverse(bd_laplacian* op, void* diag_inv_dev, void* stream);
+/* w[i] = x[i] * y[i] over n entries (pointwise_mult, src/vector.hpp:266-285). */
+int bd_pointwise_mult(int scalar_bits, int64_t n, const void* x, const void* y, void* w, void* stream);
+/* CG with z = D^-1 r: p0 = z0, alpha = (r.z)/(p.Ap), beta = (r.z)_new/(r.z), p = beta p + z; stops when
+ * (r.z)/(r.z)_0 < rtol^2 (the reference's test on its own `rnorm`, src/cg.hpp:162, which is r.z once p0 = z0).
+ * Arguments as bd_cg_solve plus the inverse diagonal. */
+int bd_cg_solve_jacobi(bd_laplacian* op, bd_halo* halo, bd_comm* comm, void* x_dev, const void* b_dev,
+                       const void* diag_inv_dev, int max_iter, double rtol, int* iterations, void* stream);
+
 /* Global inner product / l2 norm over owned entries, synchronous, host result
  * (inner_product + MPI_Allreduce, src/vector.hpp:159-176; norm, :196-218). */
 int bd_inner_product(bd_comm* comm, int scalar_bits, int64_t n_owned, const void* a, const void* b,

@@ -210,3 +210,40 @@ def cg_solve(apply, x, b, max_iter, rtol=0.0, n_owned=None, dot=None, scatter=No
             break
         p[:n] = p[:n] * beta + r[:n]
     return k
+
+
+def pcg_solve_jacobi(apply, x, b, diag_inv, max_iter, rtol=0.0, n_owned=None, dot=None, scatter=None):
+    """Jacobi-preconditioned CG: the reference's cg_solve (src/cg.hpp:89-169) with the step its comment at :165
+    names, "p <- beta*p + M^-1(r)", M^-1 = the inverse diagonal (compute_diag_inv, src/csr.hpp:79-107) applied
+    with pointwise_mult (src/vector.hpp:266-285).  With p0 = z0 the reference's `rnorm = inner_product(p, r)`
+    (:112) is r.z, which is what alpha, beta and the rtol test use."""
+    n = len(x) if n_owned is None else n_owned
+    if dot is None:
+        dot = lambda a, c: float(np.dot(a[:n], c[:n]))
+    y = np.zeros_like(x)
+    apply(x, y)
+    r = np.zeros_like(x)
+    r[:n] = -1 * y[:n] + b[:n]
+    p = np.zeros_like(x)
+    z = np.zeros_like(x)
+    p[:n] = diag_inv[:n] * r[:n]
+    rz0 = dot(p, r)
+    rz = rz0
+    rtol2 = rtol * rtol
+    k = 0
+    while k < max_iter:
+        k += 1
+        if scatter is not None:
+            scatter(p)
+        apply(p, y)
+        alpha = rz / dot(p, y)
+        x[:n] = p[:n] * alpha + x[:n]
+        r[:n] = y[:n] * (-alpha) + r[:n]
+        z[:n] = diag_inv[:n] * r[:n]
+        rz_new = dot(r, z)
+        beta = rz_new / rz
+        rz = rz_new
+        if rz / rz0 < rtol2:
+            break
+        p[:n] = p[:n] * beta + z[:n]
+    return k
