@@ -304,7 +304,7 @@ def reference_gpu_kernel_leg(bd, degree, qmode, dtype, ndofs, steps):
 
 
 # ----------------------------------------------------------------------------- our arm
-FP64_PEAK_TFLOPS = 37.1   # DMMA m8n8k4 rate measured on a B200 by scripts/microbench/fp64_rates.cu (DFMA: 34.0)
+FP64_PEAKS = None   # (DFMA, DMMA) TFLOP/s measured by bd_fp64_peak at the start of the run
 
 
 class Ctx:
@@ -374,21 +374,34 @@ def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, samp
     kernel_s = ctx.max(kernel_ms / 1e3 / steps)
     achieved = bytes_apply / kernel_s / 1e9
     gflops = algorithmic_flops_per_cell(degree, nq, qmode) * mesh.ncells / kernel_s / 1e9
-    roofline = {
-        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": load_traffic(degree, qmode, bits, mode, mesh.ncells), "peak_source": peak_src,
-        "frac_of_8TBs_nominal": achieved / 8000.0, "kernel": op.describe(), "geometry": mode,
+    hbm = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+           "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0}
+    common = {
+        "traffic": load_traffic(degree, qmode, bits, mode, mesh.ncells), "kernel": op.describe(), "geometry": mode,
         "kernel_ms_per_apply": 1e3 * kernel_s, "kernel_launches_per_apply": kernel_launches // steps,
         "algorithmic_bytes_per_apply": bytes_apply, "algorithmic_bytes_per_dof": bytes_apply / mesh.ndofs_local,
+        "algorithmic_flops_per_dof": algorithmic_flops_per_cell(degree, nq, qmode) * mesh.ncells / mesh.ndofs_local,
         "fp_gflops_algorithmic": gflops,
     }
-    if bits == 64:
-        roofline["fp64_pipe"] = {"achieved_tflops_algorithmic": gflops / 1e3, "peak_tflops": FP64_PEAK_TFLOPS,
-                                 "frac": gflops / 1e3 / FP64_PEAK_TFLOPS,
-                                 "peak_source": "scripts/microbench/fp64_rates.cu on a B200 (round 1): DMMA 37.1, DFMA 34.0"}
-    if mode != "precomputed":
-        roofline["note"] = ("geometry on the fly: no G stream, the kernel is bound by the fp64 pipe (fp64_pipe), not by "
-                            "HBM; `frac` is still its algorithmic bytes over the HBM peak")
+    fp = None
+    if FP64_PEAKS is not None:
+        # kernels with fp64 arithmetic: DMMA for nq = 7, 8 (also with float storage), DFMA for fp64 otherwise
+        dmma_kernel = nq in (7, 8) and ("mma8" in common["kernel"])
+        if bits == 64 or dmma_kernel:
+            pk = FP64_PEAKS[1] if dmma_kernel else FP64_PEAKS[0]
+            fp = {"bound": "fp64 " + ("tensor (DMMA m8n8k4)" if dmma_kernel else "pipe (DFMA)"),
+                  "achieved": gflops / 1e3, "peak": pk, "unit": "TFLOP/s", "frac": gflops / 1e3 / pk,
+                  "peak_source": "measured in this run by bd_fp64_peak (dependent-chain-free DFMA / DMMA loops, "
+                                 "csrc/peaks.cu); MEASURED_PEAKS.json has no fp64 figure",
+                  "note": "achieved = ALGORITHMIC flops (SURVEY.md section 8d) / kernel time; the kernels execute more "
+                          "(idle lanes, padding), so the pipe itself is busier than this fraction"}
+    if mode == "precomputed" or fp is None:
+        roofline = dict(hbm, **common)
+        roofline["fp64"] = fp
+    else:
+        # geometry on the fly: no G stream; the fp64 pipe, not HBM, bounds the kernel
+        roofline = dict(fp, **common)
+        roofline["hbm"] = hbm
     return {"value": mesh.ndofs_global * steps / (1e9 * secs), "ms_per_step": 1e3 * secs / steps, "secs": secs,
             "roofline": roofline, "clocks": clocks, "launches": kernel_launches, "geometry": mode}
 
@@ -573,6 +586,8 @@ def main():
     comm = bd.Comm.from_torch_distributed() if world > 1 else None
     ctx = Ctx(torch, dist, rank, world, comm)
 
+    global FP64_PEAKS
+    FP64_PEAKS = bd.fp64_peak()
     dtype = np.float64 if args.float == 64 else np.float32
     tsize = args.float // 8
     degree, qmode = args.degree, args.qmode
@@ -631,7 +646,7 @@ def main():
                                                      args.geometry, args.geom_perturb_fact)
         leg = action_leg(ctx, bd, mesh0, op0, u0, y0, max(3, args.steps // 2), args.warmup, degree, 0, args.float)
         gpu_q0 = {"value": leg["value"], "unit": "GDoF/s", "ms_per_step": leg["ms_per_step"],
-                  "roofline_frac": leg["roofline"]["frac"], "geometry": leg["geometry"], "kernel": leg["roofline"]["kernel"],
+                  "roofline_frac": leg["roofline"]["frac"], "roofline_bound": leg["roofline"]["bound"], "geometry": leg["geometry"], "kernel": leg["roofline"]["kernel"],
                   "note": "same mesh and degree at qmode 0, the only mode the reference CPU kernel supports"}
         del op0, mesh0, halo0, u0, y0
     else:
@@ -697,6 +712,7 @@ def main():
             "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic", "config": cfg,
             "roofline": head["roofline"], "cpu_baseline": cpu, "gpu_qmode0": gpu_q0, "e2e": e2e, "cg": cg,
             "variants": variants, "q6": q6, "parity": parity, "reference_gpu_kernel": ref_gpu,
+            "fp64_peaks_measured_tflops": {"dfma": FP64_PEAKS[0], "dmma": FP64_PEAKS[1]},
             "gpu_launches": gpu_launches, "clocks": head["clocks"], "u_norm": unorm, "y_norm": ynorm,
         }
         print(json.dumps(line), flush=True)

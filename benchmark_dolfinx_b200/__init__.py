@@ -96,6 +96,13 @@ def debug_set_max_grid(max_ctas: int) -> None:
     check(lib.bd_debug_set_max_grid(int(max_ctas)))
 
 
+def fp64_peak():
+    """(DFMA, DMMA) TFLOP/s measured on the current device."""
+    a, b = C.c_double(), C.c_double()
+    check(lib.bd_fp64_peak(C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
 def compute_mesh_size(ndofs_global: int, degree: int):
     """src/mesh.cpp:117-152."""
     out = (C.c_int64 * 3)()

@@ -72,6 +72,7 @@ _V = C.c_void_p
 PROTOTYPES = {
     "bd_last_error": (C.c_char_p, []),
     "bd_debug_set_max_grid": (C.c_int, [C.c_int]),
+    "bd_fp64_peak": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "bd_device_information": (C.c_int, [C.c_char_p, C.c_size_t]),
     "bd_laplacian_create": (C.c_int, [C.POINTER(LaplacianDesc), C.POINTER(_V)]),
     "bd_laplacian_destroy": (C.c_int, [_V]),

@@ -236,11 +236,12 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
                            "element in tensor-product vertex order and nq <= 8 (nq = %d)", op->nq));
   if (otf_possible && !want_pre)
     TRY(d->scalar_bits == 64 ? count_nonaffine<double>(op) : count_nonaffine<float>(op));
-  // default: the shortcut kernel when every cell is a parallelepiped (no G stream at all), a stored G otherwise
-  // (measured: the general on-the-fly kernel roughly ties with streaming G in fp64)
+  // default: the shortcut kernel when every cell is a parallelepiped and it is the measured-faster choice for this
+  // (scalar type, nq) (otf_preferred); a stored G otherwise -- for general cells rebuilding G per point loses to
+  // streaming it (Q3 fp64 18.6 vs 20.1, Q6 26.8 vs 35.0, Q3 fp32 26.0 vs 34.8 GDoF/s)
   if (want_otf)
     op->geom_mode = op->n_nonaffine == 0 ? 1 : 2;
-  else if (!want_pre && otf_possible && op->n_nonaffine == 0)
+  else if (!want_pre && otf_possible && op->n_nonaffine == 0 && otf_preferred(op->scalar_bits, op->degree, op->nq))
     op->geom_mode = 1;
   else
     op->geom_mode = 0;

@@ -220,8 +220,6 @@ int launch_stiffness_slab(const StiffnessArgs& a)
 }
 
 // Slab kernel with on-the-fly geometry (stiffness_slab_otf.cuh), nq <= 6.
-int otf_minb_variant(); // TEMPORARY (A/B of the register cap): env BD_OTF_MINB
-
 template <typename T, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int MINB = 1>
 int launch_stiffness_slab_otf_cfg(const StiffnessArgs& a)
 {
@@ -283,12 +281,13 @@ int launch_stiffness_slab_otf(const StiffnessArgs& a)
     return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");
   else
   {
-    // TEMPORARY A/B: BD_OTF_MINB=12 caps the kernel at 168 registers (12 one-warp CTAs per SM)
-    if (otf_minb_variant() == 12)
-      return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, 12>(a)
-                              : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 12>(a);
-    return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true>(a)
-                            : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false>(a);
+    // Register cap (measured, profiles/r2_onthefly_*_ab.txt): 168 registers = 12 one-warp CTAs per SM wins for the
+    // fp64 qmode-1 kernels at nq = 4, 5 (Q3: 30.3 -> 31.2 GDoF/s, Q2: 22.8 -> 24.3); it loses where the kernel then
+    // spills (nq = 6: 31.9 -> 22.4) or where Phi = I leaves the registers free anyway (Q4 qmode 0: 69.0 -> 61.5).
+    // The general-cell kernel runs uncapped (capped it spills: Q3 perturbed 18.6 -> 15.2 GDoF/s).
+    constexpr int MINB = (sizeof(T) == 8 && !IDENTITY && (NQ == 4 || NQ == 5)) ? 12 : 1;
+    return a.geom_mode == 1 ? launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, true, MINB>(a)
+                            : launch_stiffness_slab_otf_cfg<T, P, NQ, IDENTITY, false, 1>(a);
   }
 }
 
@@ -443,6 +442,16 @@ int launch_stiffness_otf_f32_q1(int degree, const StiffnessArgs& a);
 int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const StiffnessArgs& a);
 // on-the-fly geometry exists for this (degree, nq)?
 inline bool otf_supported(int degree, int nq) { return nq >= 2 && nq <= 8 && (nq == degree + 1 || nq == degree + 2); }
+// ... and is the measured-faster choice on a mesh of parallelepipeds (profiles/r2_onthefly_*_ab.txt, one B200)?
+//   nq <= 6 (slab kernel): yes for both scalar types (fp64 1.45-1.7x, fp32 1.3x over streaming G);
+//   nq = 8, fp64 (DMMA kernel): a tie at qmode 1 (34.4 vs 34.4 GDoF/s: that kernel is bound by its arithmetic,
+//           not by the G stream), 1.35x at qmode 0 -> on the fly (56 GB less memory, no G precompute);
+//   nq = 7, fp64: stored G wins at qmode 1 (24.6 vs 21.8 GDoF/s); fp32 with nq >= 7: the pencil kernels with a
+//           stored G win (50.3 vs 34.8 GDoF/s at Q6) -> stored G.
+inline bool otf_preferred(int scalar_bits, int degree, int nq)
+{
+  return otf_supported(degree, nq) && (nq <= 6 || (nq == 8 && scalar_bits == 64));
+}
 
 // in geometry.cu
 // G layouts: 0 = reference [cell][6][nq^3] (pencil kernel), 1 = slab (stiffness_slab.cuh), 2 = DMMA

@@ -70,6 +70,8 @@ int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const Stif
   return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers nq = 7 and nq = 8 only");
 }
 
+// MINB: 3 CTAs of 4 warps per SM for the affine-cell kernel (163 registers, no spills); the general-cell kernel
+// runs uncapped (238 registers, 2 CTAs per SM): capped at 168 it spills and is 2.5x slower (measured).
 template <typename TS, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int MINB = 1, bool PREFETCH = true>
 static int launch_mma8_otf(const StiffnessArgs& a)
 {
@@ -121,17 +123,11 @@ int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const 
 #define BD_MMA8_OTF_CASE(P, NQ, ID)                                                                \
   if (degree == P && identity == ID)                                                               \
   {                                                                                                \
-    if (scalar_bits == 64 && otf_minb_variant() == 30)                                             \
-      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true, 3, false>(a)              \
-                              : launch_mma8_otf<double, P, NQ, ID, false, 3, false>(a);            \
-    if (scalar_bits == 64 && otf_minb_variant() == 3)                                              \
-      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true, 3>(a)                     \
-                              : launch_mma8_otf<double, P, NQ, ID, false, 3>(a);                   \
     if (scalar_bits == 64)                                                                         \
-      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true>(a)                        \
-                              : launch_mma8_otf<double, P, NQ, ID, false>(a);                      \
-    return a.geom_mode == 1 ? launch_mma8_otf<float, P, NQ, ID, true>(a)                           \
-                            : launch_mma8_otf<float, P, NQ, ID, false>(a);                         \
+      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true, 3>(a)                     \
+                              : launch_mma8_otf<double, P, NQ, ID, false, 1>(a);                   \
+    return a.geom_mode == 1 ? launch_mma8_otf<float, P, NQ, ID, true, 3>(a)                        \
+                            : launch_mma8_otf<float, P, NQ, ID, false, 1>(a);                      \
   }
   BD_MMA8_OTF_CASE(6, 8, false)
   BD_MMA8_OTF_CASE(7, 8, true)

@@ -44,6 +44,11 @@ const char* bd_last_error(void);
  * which is where the benchmark sizes spend all their time.  Process-wide; not for production. */
 int bd_debug_set_max_grid(int max_ctas);
 
+/* Measured fp64 arithmetic peaks of the current device in TFLOP/s (plain DFMA and tensor-core DMMA m8n8k4
+ * loops without dependent chains, ~50 ms): roofline denominators for the compute-bound variants.  No
+ * counterpart in the reference. */
+int bd_fp64_peak(double* dfma_tflops, double* dmma_tflops);
+
 /* Library / device banner (replaces get_device_information, src/util.cpp:10-52).
  * Writes at most `n` bytes including the terminator. */
 int bd_device_information(char* buf, size_t n);
