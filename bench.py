@@ -355,6 +355,8 @@ def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, samp
     ctx.barrier()
     sampler = ClockSampler(local_rank) if (sample_clocks and ctx.rank == 0) else None
     op.profile(True)
+    if op.halo is not None:
+        op.halo.profile(True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(steps):
@@ -364,6 +366,16 @@ def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, samp
     secs = ctx.max(ev0.elapsed_time(ev1) / 1e3)
     kernel_ms, kernel_launches = op.profile_read()
     op.profile(False)
+    halo_rec = None
+    if op.halo is not None:
+        h = op.halo.profile_read()
+        op.halo.profile(False)
+        napp = max(1, h["applications"])
+        halo_rec = {"pack_ms": ctx.max(h["pack_ms"] / napp), "exchange_ms": ctx.max(h["exchange_ms"] / napp),
+                    "exposed_ms": ctx.max(h["exposed_ms"] / napp), "ghost_dofs_max": int(ctx.max(float(mesh.nghost))),
+                    "note": "per operator application, max over ranks; exposed = how long the ghost values arrived "
+                            "after the interior-cell kernel had finished (CUDA events on the plan's stream and the "
+                            "caller's stream)"}
     clocks = sampler.stop() if sampler is not None else None
     mode = op.geometry_mode()[0]
     peak, peak_src = measured_peak_gbs()
@@ -403,7 +415,7 @@ def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, samp
         roofline = dict(fp, **common)
         roofline["hbm"] = hbm
     return {"value": mesh.ndofs_global * steps / (1e9 * secs), "ms_per_step": 1e3 * secs / steps, "secs": secs,
-            "roofline": roofline, "clocks": clocks, "launches": kernel_launches, "geometry": mode}
+            "roofline": roofline, "clocks": clocks, "launches": kernel_launches, "geometry": mode, "halo": halo_rec}
 
 
 def cg_leg(ctx, bd, mesh, op, u, steps, warmup, bytes_apply, tsize):
@@ -632,6 +644,7 @@ def main():
                                                  leg["roofline"]["algorithmic_bytes_per_apply"], tsize)
             variants[leg["geometry"]] = {"value": leg["value"], "ms_per_step": leg["ms_per_step"],
                                          "roofline": leg["roofline"], "cg": cg2 and cg2["value"], "y_norm": yn2,
+                                         "halo": leg["halo"],
                                          "rel_diff_y_norm_vs_headline": abs(yn2 - ynorm) / ynorm, "headline": False}
             gpu_launches += args.steps * leg["roofline"]["kernel_launches_per_apply"]
             del op2
@@ -662,6 +675,7 @@ def main():
         leg = action_leg(ctx, bd, mesh6, op6, u6, y6, args.steps, args.warmup, 6, 1, 64)
         q6 = {"value": leg["value"], "unit": "GDoF/s", "ms_per_step": leg["ms_per_step"], "roofline": leg["roofline"],
               "geometry": leg["geometry"], "ndofs_global": mesh6.ndofs_global, "mesh_cells": n6, "setup_seconds": t6,
+              "halo": leg["halo"],
               "y_norm": bd.norm(y6, mesh6.ndofs_owned, comm),
               "cg": None if args.no_cg else cg_leg(ctx, bd, mesh6, op6, u6, args.steps, args.warmup,
                                                    leg["roofline"]["algorithmic_bytes_per_apply"], 8)}
@@ -711,7 +725,7 @@ def main():
             "scaling": "strong" if args.ndofs_global else "weak",
             "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic", "config": cfg,
             "roofline": head["roofline"], "cpu_baseline": cpu, "gpu_qmode0": gpu_q0, "e2e": e2e, "cg": cg,
-            "variants": variants, "q6": q6, "parity": parity, "reference_gpu_kernel": ref_gpu,
+            "halo": head["halo"], "variants": variants, "q6": q6, "parity": parity, "reference_gpu_kernel": ref_gpu,
             "fp64_peaks_measured_tflops": {"dfma": FP64_PEAKS[0], "dmma": FP64_PEAKS[1]},
             "gpu_launches": gpu_launches, "clocks": head["clocks"], "u_norm": unorm, "y_norm": ynorm,
         }

@@ -299,6 +299,16 @@ class Halo:
         self.begin(x, stream)
         self.end(stream)
 
+    def profile(self, enable: bool):
+        """Time pack / exchange / exposed wait of every operator application that uses this plan."""
+        check(lib.bd_halo_profile(self._h, int(enable)))
+
+    def profile_read(self):
+        """dict(pack_ms, exchange_ms, exposed_ms, applications) summed since the last read."""
+        a, b, c, n = C.c_double(), C.c_double(), C.c_double(), C.c_int64()
+        check(lib.bd_halo_profile_read(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(n)))
+        return {"pack_ms": a.value, "exchange_ms": b.value, "exposed_ms": c.value, "applications": n.value}
+
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h and lib is not None:          # module globals may be gone at interpreter exit

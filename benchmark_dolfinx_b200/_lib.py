@@ -105,6 +105,9 @@ PROTOTYPES = {
     "bd_halo_destroy": (C.c_int, [_V]),
     "bd_halo_begin": (C.c_int, [_V, _V, _V]),
     "bd_halo_end": (C.c_int, [_V, _V]),
+    "bd_halo_profile": (C.c_int, [_V, C.c_int]),
+    "bd_halo_profile_read": (C.c_int, [_V, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                       C.POINTER(C.c_int64)]),
     "bd_laplacian_apply_halo": (C.c_int, [_V, _V, _V, _V, _V]),
     "bd_cg_solve": (C.c_int, [_V, _V, _V, _V, _V, C.c_int, C.c_double, C.POINTER(C.c_int), _V]),
     "bd_laplacian_diagonal_inverse": (C.c_int, [_V, _V, _V]),

@@ -213,7 +213,12 @@ extern "C" int bd_halo_create(bd_comm* comm, int scalar_bits, int64_t n_owned, i
     return bail(rc);
   if ((rc = h->send_buf.alloc(static_cast<size_t>(tot > 0 ? tot : 1) * (scalar_bits / 8))) != BD_SUCCESS)
     return bail(rc);
-  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess
+  // Highest priority: the NCCL kernel must get its SM resources before the persistent interior-cell kernel, which
+  // is released by the same event and otherwise fills every SM until it ends (the exchange then only starts in that
+  // kernel's tail: 1.6 ms exposed per application on 2 GPUs in round 1).
+  int prio_lo = 0, prio_hi = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+  if (cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess
       || cudaEventCreateWithFlags(&h->ev_ready, cudaEventDisableTiming) != cudaSuccess
       || cudaEventCreateWithFlags(&h->ev_done, cudaEventDisableTiming) != cudaSuccess)
     return bail(fail(BD_ERR_CUDA, "halo stream/event creation failed"));
@@ -242,6 +247,8 @@ extern "C" int bd_halo_destroy(bd_halo* h)
 {
   if (!h)
     return BD_SUCCESS;
+  for (cudaEvent_t e : h->prof_events)
+    cudaEventDestroy(e);
   if (h->ev_ready)
     cudaEventDestroy(h->ev_ready);
   if (h->ev_done)
@@ -252,17 +259,24 @@ extern "C" int bd_halo_destroy(bd_halo* h)
   return BD_SUCCESS;
 }
 
-extern "C" int bd_halo_begin(bd_halo* h, void* x_dev, void* stream_)
+namespace
 {
-  BD_REQUIRE(h && x_dev, "bd_halo_begin: null argument");
-  cudaStream_t stream = as_stream(stream_);
-  // the exchange starts once everything already queued on `stream` (the producer of x) is done
+// `mark` (optional): events recorded on the side stream right before / after the NCCL group.
+int halo_begin_impl(bd_halo* h, void* x_dev, cudaStream_t stream, cudaEvent_t mark0, cudaEvent_t mark1)
+{
+  const bool multi = h->comm->nranks > 1;
+  const size_t ts = static_cast<size_t>(h->scalar_bits / 8);
+  // The pack runs on the caller's stream, ahead of the event: the exchange proper (one NCCL kernel) is then
+  // ready at the same instant as whatever the caller queues next, and wins the SMs by stream priority.
+  if (multi)
+    BD_CHECK(bd_pack(h->scalar_bits, h->n_send_total, h->send_idx.ptr, x_dev, h->send_buf.ptr, stream));
+  // the exchange starts once everything already queued on `stream` (the producer of x, the pack) is done
   BD_CUDA_CHECK(cudaEventRecord(h->ev_ready, stream));
   BD_CUDA_CHECK(cudaStreamWaitEvent(h->stream, h->ev_ready, 0));
-  if (h->comm->nranks > 1)
+  if (mark0)
+    BD_CUDA_CHECK(cudaEventRecord(mark0, h->stream));
+  if (multi)
   {
-    const size_t ts = static_cast<size_t>(h->scalar_bits / 8);
-    BD_CHECK(bd_pack(h->scalar_bits, h->n_send_total, h->send_idx.ptr, x_dev, h->send_buf.ptr, h->stream));
     const ncclDataType_t dt = h->scalar_bits == 64 ? ncclFloat64 : ncclFloat32;
     ncclComm_t nc = static_cast<ncclComm_t>(h->comm->nccl);
     NcclApi& api = nccl_api();
@@ -287,7 +301,50 @@ extern "C" int bd_halo_begin(bd_halo* h, void* x_dev, void* stream_)
     if (h->use_unpack)
       BD_CHECK(bd_unpack(h->scalar_bits, h->n_ghost, h->unpack_idx.ptr, h->recv_buf.ptr, ghost_seg, h->stream));
   }
+  if (mark1)
+    BD_CUDA_CHECK(cudaEventRecord(mark1, h->stream));
   BD_CUDA_CHECK(cudaEventRecord(h->ev_done, h->stream));
+  return BD_SUCCESS;
+}
+} // namespace
+
+extern "C" int bd_halo_begin(bd_halo* h, void* x_dev, void* stream_)
+{
+  BD_REQUIRE(h && x_dev, "bd_halo_begin: null argument");
+  return halo_begin_impl(h, x_dev, as_stream(stream_), nullptr, nullptr);
+}
+
+extern "C" int bd_halo_profile(bd_halo* h, int enable)
+{
+  BD_REQUIRE(h, "bd_halo_profile: null plan");
+  h->profile = enable != 0;
+  h->prof_used = 0;
+  return BD_SUCCESS;
+}
+
+extern "C" int bd_halo_profile_read(bd_halo* h, double* pack_ms, double* exchange_ms, double* exposed_ms,
+                                    int64_t* applications)
+{
+  BD_REQUIRE(h && pack_ms && exchange_ms && exposed_ms && applications, "bd_halo_profile_read: null argument");
+  double pk = 0, ex = 0, xp = 0;
+  for (size_t i = 0; i + 3 < h->prof_used; i += 4)
+  {
+    cudaEvent_t* e = h->prof_events.data() + i;
+    BD_CUDA_CHECK(cudaEventSynchronize(e[2]));
+    BD_CUDA_CHECK(cudaEventSynchronize(e[3]));
+    float a = 0, b = 0, c = 0;
+    BD_CUDA_CHECK(cudaEventElapsedTime(&a, e[0], e[1])); // main: before pack -> side: exchange may start
+    BD_CUDA_CHECK(cudaEventElapsedTime(&b, e[1], e[2])); // side: the NCCL group (+ unpack)
+    BD_CUDA_CHECK(cudaEventElapsedTime(&c, e[3], e[2])); // interior kernel done -> ghosts ready (> 0: exposed)
+    pk += a;
+    ex += b;
+    xp += c > 0 ? c : 0;
+  }
+  *pack_ms = pk;
+  *exchange_ms = ex;
+  *exposed_ms = xp;
+  *applications = static_cast<int64_t>(h->prof_used / 4);
+  h->prof_used = 0;
   return BD_SUCCESS;
 }
 
@@ -307,8 +364,26 @@ extern "C" int bd_laplacian_apply_halo(bd_laplacian* op, bd_halo* halo, void* in
   BD_REQUIRE(halo->n_owned + halo->n_ghost == op->ndofs && halo->scalar_bits == op->scalar_bits,
              "halo plan does not match the operator");
   // impl_operator (src/laplacian.hpp:281-349): begin scatter, lcells, end scatter, bcells
-  BD_CHECK(bd_halo_begin(halo, in_dev, stream));
+  if (!halo->profile)
+  {
+    BD_CHECK(bd_halo_begin(halo, in_dev, stream));
+    BD_CHECK(bd_laplacian_apply_part(op, 0, in_dev, out_dev, stream));
+    BD_CHECK(bd_halo_end(halo, stream));
+    return bd_laplacian_apply_part(op, 1, in_dev, out_dev, stream);
+  }
+  if (halo->prof_used + 4 > halo->prof_events.size())
+    for (int i = 0; i < 4; ++i)
+    {
+      cudaEvent_t e;
+      BD_CUDA_CHECK(cudaEventCreate(&e));
+      halo->prof_events.push_back(e);
+    }
+  cudaEvent_t* e = halo->prof_events.data() + halo->prof_used;
+  BD_CUDA_CHECK(cudaEventRecord(e[0], as_stream(stream)));
+  BD_CHECK(halo_begin_impl(halo, in_dev, as_stream(stream), e[1], e[2]));
   BD_CHECK(bd_laplacian_apply_part(op, 0, in_dev, out_dev, stream));
+  BD_CUDA_CHECK(cudaEventRecord(e[3], as_stream(stream)));
+  halo->prof_used += 4;
   BD_CHECK(bd_halo_end(halo, stream));
   return bd_laplacian_apply_part(op, 1, in_dev, out_dev, stream);
 }

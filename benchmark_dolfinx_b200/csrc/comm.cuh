@@ -30,6 +30,12 @@ struct bd_halo
   cudaStream_t stream = nullptr;      // exchange runs here, overlapped with the lcells kernel
   cudaEvent_t ev_ready = nullptr;     // producer of x done
   cudaEvent_t ev_done = nullptr;      // ghosts of x up to date
+  // optional timing of the exchange inside bd_laplacian_apply_halo (bd_halo_profile): per application four
+  // events -- main stream before the pack, side stream before / after the NCCL group, main stream after the
+  // interior-cell kernel -- from which pack, exchange and exposed (not hidden behind the interior cells) times follow
+  bool profile = false;
+  std::vector<cudaEvent_t> prof_events;
+  size_t prof_used = 0;
 };
 
 namespace bd

@@ -245,6 +245,15 @@ int bd_halo_destroy(bd_halo* halo);
  * own stream after the work already queued on `stream`; end: make `stream` wait. */
 int bd_halo_begin(bd_halo* halo, void* x_dev, void* stream);
 int bd_halo_end(bd_halo* halo, void* stream);
+/* Optional timing of the exchange inside bd_laplacian_apply_halo (no counterpart in the reference, whose
+ * scatter is synchronous, src/vector.hpp:117,146): while enabled, every application records CUDA events around
+ * the pack, the NCCL send/recv group and the interior-cell kernel.  bd_halo_profile_read sums, over the
+ * applications since the last read: pack_ms (pack kernel, on the caller's stream), exchange_ms (the NCCL group on
+ * the plan's stream) and exposed_ms (how long the ghost values arrived AFTER the interior-cell kernel had
+ * finished, i.e. the part of the exchange that was not hidden). */
+int bd_halo_profile(bd_halo* halo, int enable);
+int bd_halo_profile_read(bd_halo* halo, double* pack_ms, double* exchange_ms, double* exposed_ms,
+                         int64_t* applications);
 
 /* out = A in including the halo exchange of `in`, overlapped with the lcells
  * kernel exactly as impl_operator does (src/laplacian.hpp:281-349).  `halo` may
