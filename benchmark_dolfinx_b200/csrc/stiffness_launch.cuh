@@ -160,6 +160,9 @@ int launch_stiffness_slab_tma(const StiffnessArgs& a)
   constexpr int NSTAGE = (NQ == 7) ? 2 : TU::NSTAGE;
   // nq <= 5: ring of 2 slots, 1 warp per CTA (7 warps/SM at Q3 fp64) measured ahead of 3 slots / 2 warps per
   // CTA (15.2 vs 16.1 ms at Q3/300M, round 1)
+  // Round 2 A/B at Q3 / 300M dofs fp64 (profiles/r2_ring_ab.txt): finer slots with more of them in flight (one q0 row
+  // per slot, rings of 4 / 6 / 8 / 10 slots, 8-9 CTAs per SM) are slower (17.2-18.1 GDoF/s) than 2 whole-slice slots
+  // (19.8), and so is a third whole-slice slot (18.7): the per-copy cost and the lost occupancy outweigh the deeper queue.
   // the gather prefetch needs 3 * nd^2 extra registers: affordable up to nd = 5
   constexpr bool PF = TU::PREFETCH || (NQ == 6 && P + 1 <= 5);
   return launch_stiffness_slab_tma_cfg<T, P, NQ, IDENTITY, NSTAGE, TU::Q0C, TU::WARPS, PF>(a);
@@ -444,13 +447,14 @@ int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const 
 inline bool otf_supported(int degree, int nq) { return nq >= 2 && nq <= 8 && (nq == degree + 1 || nq == degree + 2); }
 // ... and is the measured-faster choice on a mesh of parallelepipeds (profiles/r2_onthefly_*_ab.txt, one B200)?
 //   nq <= 6 (slab kernel): yes for both scalar types (fp64 1.45-1.7x, fp32 1.3x over streaming G);
-//   nq = 8, fp64 (DMMA kernel): a tie at qmode 1 (34.4 vs 34.4 GDoF/s: that kernel is bound by its arithmetic,
-//           not by the G stream), 1.35x at qmode 0 -> on the fly (56 GB less memory, no G precompute);
-//   nq = 7, fp64: stored G wins at qmode 1 (24.6 vs 21.8 GDoF/s); fp32 with nq >= 7: the pencil kernels with a
-//           stored G win (50.3 vs 34.8 GDoF/s at Q6) -> stored G.
+//   nq = 8, fp64 (DMMA kernel): 37.8 vs 34.4 GDoF/s at Q6 qmode 1 (that kernel is bound by its arithmetic, not by
+//           the G stream), 78.2 vs 51.4 at Q7 qmode 0 -> on the fly (and 56 GB less memory, no G precompute);
+//   nq = 7, fp64: on the fly wins with Phi = I (Q6 qmode 0: 59.5 vs 52.9), stored G wins at qmode 1 (Q5: 24.6 vs 23.4);
+//   fp32 with nq >= 7: the pencil kernels with a stored G win (50.3 vs 34.8 GDoF/s at Q6) -> stored G.
 inline bool otf_preferred(int scalar_bits, int degree, int nq)
 {
-  return otf_supported(degree, nq) && (nq <= 6 || (nq == 8 && scalar_bits == 64));
+  return otf_supported(degree, nq)
+         && (nq <= 6 || (scalar_bits == 64 && (nq == 8 || (nq == 7 && nq == degree + 1))));
 }
 
 // in geometry.cu

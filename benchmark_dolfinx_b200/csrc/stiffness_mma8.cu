@@ -70,9 +70,11 @@ int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const Stif
   return fail(BD_ERR_UNSUPPORTED, "the DMMA kernel covers nq = 7 and nq = 8 only");
 }
 
-// MINB: 3 CTAs of 4 warps per SM for the affine-cell kernel (163 registers, no spills); the general-cell kernel
-// runs uncapped (238 registers, 2 CTAs per SM): capped at 168 it spills and is 2.5x slower (measured).
-template <typename TS, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int MINB = 1, bool PREFETCH = true>
+// MINB: 3 CTAs of 4 warps per SM for the affine-cell kernel (168 registers, 16 bytes of spills); the general-cell
+// kernel runs uncapped (238 registers, 2 CTAs per SM): capped at 168 it spills and is 2.5x slower (measured).
+// FE: a scheduling fence every 4 y-tiles for the affine-cell kernel (measured at Q6 / 500M dofs: a fence per tile
+// 34.5, every 2 tiles 37.1, every 4 tiles 37.8 GDoF/s; every 4 or 8 tiles at 2 CTAs per SM 33.7 / 35.5).
+template <typename TS, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int MINB = 1, bool PREFETCH = true, int FE = 1>
 static int launch_mma8_otf(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
@@ -83,7 +85,7 @@ static int launch_mma8_otf(const StiffnessArgs& a)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d || !a.pts1d)
     return fail(BD_ERR_INVALID_ARGUMENT, "on-the-fly geometry needs the masked dofmap, vertices and 1-D rule");
-  auto kernel = stiffness_mma8_otf_kernel<TS, P, NQ, IDENTITY, kWarps, AFFINE_ONLY, MINB, PREFETCH>;
+  auto kernel = stiffness_mma8_otf_kernel<TS, P, NQ, IDENTITY, kWarps, AFFINE_ONLY, MINB, PREFETCH, FE>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -124,9 +126,9 @@ int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const 
   if (degree == P && identity == ID)                                                               \
   {                                                                                                \
     if (scalar_bits == 64)                                                                         \
-      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true, 3>(a)                     \
+      return a.geom_mode == 1 ? launch_mma8_otf<double, P, NQ, ID, true, 3, true, 4>(a)            \
                               : launch_mma8_otf<double, P, NQ, ID, false, 1>(a);                   \
-    return a.geom_mode == 1 ? launch_mma8_otf<float, P, NQ, ID, true, 3>(a)                        \
+    return a.geom_mode == 1 ? launch_mma8_otf<float, P, NQ, ID, true, 3, true, 4>(a)               \
                             : launch_mma8_otf<float, P, NQ, ID, false, 1>(a);                      \
   }
   BD_MMA8_OTF_CASE(6, 8, false)

@@ -39,7 +39,8 @@ __device__ __forceinline__ double2 lds_f64x2(const double* p)
   return v;
 }
 
-template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, bool AFFINE_ONLY, int MINB = 1, bool PREFETCH = true>
+template <typename TS, int P, int NQ, bool IDENTITY, int kMma8Warps, bool AFFINE_ONLY, int MINB = 1, bool PREFETCH = true,
+          int FENCE_EVERY = 1>
 __global__ void __launch_bounds__(kMma8Warps * 32, MINB)
     stiffness_mma8_otf_kernel(const TS* __restrict__ u, TS* __restrict__ y, const TS* __restrict__ xgeom,
                               const std::int32_t* __restrict__ gdofmap, const TS* __restrict__ cell_constants,
@@ -279,7 +280,8 @@ __global__ void __launch_bounds__(kMma8Warps * 32, MINB)
         R[yy][0] = R[yy][1] = 0;
         continue;
       }
-      sched_fence(fbar); // see sched_fence
+      if (yy % FENCE_EVERY == 0)
+        sched_fence(fbar); // see sched_fence
       double gx0, gx1, gz0, gz1;
       mma8_row(gx0, gx1, T[yy][0], T[yy][1], d_row, src0, src1, odd);
       mma8_col(gz0, gz1, T[yy][0], T[yy][1], d_col);

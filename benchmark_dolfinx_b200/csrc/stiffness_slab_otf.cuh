@@ -247,6 +247,9 @@ struct SlabOtfConfig
   static constexpr bool SUPPORTED = CTA_SMEM <= 226 * 1024;
 };
 
+#ifndef BD_SLAB_OTF_FENCE
+#define BD_SLAB_OTF_FENCE 1
+#endif
 template <typename T, int P, int NQ, bool IDENTITY, bool AFFINE_ONLY, int WARPS_, bool PREFETCH, int MINB = 1>
 __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     stiffness_slab_otf_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ xgeom,
@@ -473,7 +476,9 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
         by[i] = 0;
         bz[i] = 0;
       }
+#if BD_SLAB_OTF_FENCE
       sched_fence(fbar);
+#endif
       const T wrow = IDENTITY ? tab.w[q1] * w2 : T(1);
       if (zactive)
       {
