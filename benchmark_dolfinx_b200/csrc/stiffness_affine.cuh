@@ -1,0 +1,312 @@
+// Stiffness action on meshes of parallelepipeds, evaluated in dof space (degree <= 3).
+//
+// On an affine cell the geometry factor of the reference (src/geometry_gpu.hpp:113-130) is G(q) = w_q0 w_q1 w_q2 Gc
+// with a constant 3x3 matrix Gc, so the quadrature sums of stiffness_operator_gpu (src/laplacian_gpu.hpp:175-420)
+//     y = sum_{d,e} Gc[d][e] B_d^T W B_e u,     B_0 = DPhi_x (x) Phi_y (x) Phi_z, ... (DPhi = dphi1 * phi0)
+// factor direction by direction into three nd x nd matrices built once on the host from the same tables:
+//     M = Phi^T W Phi,   S = DPhi^T W DPhi,   C = DPhi^T W Phi          (W = diag of the 1-D weights)
+//     y = Gc00 S_x M_y M_z u + Gc11 M_x S_y M_z u + Gc22 M_x M_y S_z u
+//       + Gc01 (C_x C^T_y M_z + C^T_x C_y M_z) u + Gc02 (C_x M_y C^T_z + C^T_x M_y C_z) u
+//       + Gc12 (M_x C_y C^T_z + M_x C^T_y C_z) u.
+// Same terms as the quadrature loop, summed in another order (differences at rounding level; same tests, same
+// tolerances).  Grouped by the x operator it takes 13 nd^3 multiply-adds per dof plane for the y / z part and
+// 4 nd^3 for x: 4352 per Q3 cell instead of the ~9300 the quadrature-space kernel executes, and the quadrature
+// size drops out of the kernel altogether (qmode only changes M, S, C).
+//
+// Execution: a team of ND lanes owns a cell, a warp owns 32 / ND cells, every lane of a full warp works in both
+// phases.  Phase A, lane (c, i): the dof plane u[i][.][.] -> four planes P1..P4[i][.][.] (y and z contracted, Gc
+// folded in).  Exchange through shared memory (conflict-free strides found at compile time).  Phase B, lane
+// (c, j): x contraction for the column (., j, .), then scatter-add.  Only __syncwarp between the phases.
+// General (non-affine) cells never reach this kernel (the operator checks every cell at construction).
+#pragma once
+
+#include "stiffness_slab_otf.cuh"
+
+namespace bd
+{
+template <typename T, int ND>
+struct AffineTables
+{
+  T M[ND * ND]; // M[a][b] = sum_q w_q Phi[q][a] Phi[q][b]
+  T S[ND * ND]; // S[a][b] = sum_q w_q DPhi[q][a] DPhi[q][b]
+  T C[ND * ND]; // C[a][b] = sum_q w_q DPhi[q][a] Phi[q][b]
+};
+
+struct AffineStrides
+{
+  int si, sj;
+};
+
+// Strides of the exchange buffer, element (plane p, i, j, k, cell c) at p*PL + k*sk + j*sj + i*si + c:
+// phase A writes with lanes (c, i) [fixed p, j, k], phase B reads with lanes (c, j) [fixed p, i, k]; both must be
+// bank-conflict free within each group of lanes the hardware serves together (16 for 8-byte, 32 for 4-byte words).
+constexpr AffineStrides affine_strides(int nd, bool is_double)
+{
+  const int cw = 32 / nd;
+  const int nbanks = is_double ? 16 : 32, group = is_double ? 16 : 32;
+  for (int si = cw; si < cw + 33; ++si)
+    for (int sj = nd * si; sj < nd * si + 33; ++sj)
+    {
+      bool ok = true;
+      for (int pass = 0; pass < 2 && ok; ++pass)
+        for (int g0 = 0; g0 < 32 && ok; g0 += group)
+        {
+          bool used[32] = {};
+          for (int l = g0; l < g0 + group && ok; ++l)
+          {
+            const int c = l / nd, m = l % nd;
+            if (c >= cw)
+              continue;
+            const int b = (m * (pass == 0 ? si : sj) + c) % nbanks;
+            if (used[b])
+              ok = false;
+            used[b] = true;
+          }
+        }
+      if (ok)
+        return {si, sj};
+    }
+  return {cw, nd * cw};
+}
+
+template <typename T, int P, int WARPS_>
+struct AffineConfig
+{
+  static constexpr int ND = P + 1;
+  static constexpr int CW = 32 / ND;
+  static constexpr AffineStrides ST = affine_strides(ND, sizeof(T) == 8);
+  static constexpr int SI = ST.si, SJ = ST.sj, SK = ND * SJ, PL = ND * SK;
+  static constexpr int WARP_BYTES = (4 * PL * int(sizeof(T)) + 15) / 16 * 16;
+  static constexpr int WARPS = WARPS_;
+  static constexpr int THREADS = WARPS * 32;
+  static constexpr int CTA_SMEM = WARPS * WARP_BYTES;
+};
+
+template <typename T, int P, int WARPS_, int MINB>
+__global__ void __launch_bounds__(WARPS_ * 32, MINB)
+    stiffness_affine_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ xgeom,
+                            const std::int32_t* __restrict__ gdofmap, const T* __restrict__ cell_constants,
+                            const std::int32_t* __restrict__ mdofmap, const std::int32_t* __restrict__ cells,
+                            int ncells, const __grid_constant__ AffineTables<T, P + 1> tab)
+{
+  using AC = AffineConfig<T, P, WARPS_>;
+  constexpr int ND = AC::ND, CW = AC::CW, SI = AC::SI, SJ = AC::SJ, SK = AC::SK, PL = AC::PL;
+  constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int c = lane / ND;
+  const int m = lane - c * ND;
+  const bool lane_ok = c < CW;
+  T* buf = reinterpret_cast<T*>(smem_raw + warp * AC::WARP_BYTES) + (lane_ok ? c : 0);
+
+  const int nbatches = (ncells + CW - 1) / CW;
+  const int warps_total = gridDim.x * AC::WARPS;
+  const int first = blockIdx.x * AC::WARPS + warp;
+  const int my_batches = first < nbatches ? (nbatches - first + warps_total - 1) / warps_total : 0;
+
+  auto cell_of = [&](int batch) -> std::int32_t {
+    const int pos = batch * CW + c;
+    return (lane_ok && batch < nbatches && pos < ncells) ? cells[pos] : -1;
+  };
+  auto kappa_of = [&](int batch) -> T {
+    const int pos = batch * CW + c;
+    return (lane_ok && batch < nbatches && pos < ncells) ? cell_constants[pos] : T(0);
+  };
+  // phase A gathers the plane (i = m, ., .): entries m*ND2 + j*ND + k of the cell's row
+  auto load_dofs = [&](std::int32_t cell, std::int32_t (&d)[ND2]) {
+    const std::int32_t* row = cell >= 0 ? mdofmap + static_cast<std::int64_t>(cell) * ND3 + m * ND2 : nullptr;
+#pragma unroll
+    for (int t = 0; t < ND2; ++t)
+      d[t] = row ? row[t] : kBcBit; // lanes without a cell look like constrained dofs
+  };
+  auto load_values = [&](std::int32_t cell, const std::int32_t (&d)[ND2], T (&v)[ND2]) {
+#pragma unroll
+    for (int t = 0; t < ND2; ++t)
+      v[t] = cell >= 0 ? u[d[t] & 0x7fffffff] : T(0);
+  };
+  // the four vertices that span a parallelepiped: v = 0, 4, 2, 1 of the tensor-product order
+  auto load_vertex_ids = [&](std::int32_t cell, std::int32_t (&v)[4]) {
+    if (cell >= 0)
+    {
+      const int4* gd = reinterpret_cast<const int4*>(gdofmap + static_cast<std::int64_t>(cell) * 8);
+      const int4 lo = __ldg(gd), hi = __ldg(gd + 1);
+      v[0] = lo.x, v[1] = hi.x, v[2] = lo.z, v[3] = lo.y;
+    }
+    else
+      v[0] = v[1] = v[2] = v[3] = -1;
+  };
+
+  std::int32_t dof[ND2], vid[4];
+  T ul[ND2];
+  std::int32_t cell_cur = my_batches > 0 ? cell_of(first) : -1;
+  std::int32_t cell_next = my_batches > 1 ? cell_of(first + warps_total) : -1;
+  T kappa = my_batches > 0 ? kappa_of(first) : T(0);
+  load_vertex_ids(cell_cur, vid);
+  load_dofs(cell_cur, dof);
+  load_values(cell_cur, dof, ul);
+
+  for (int kb = 0; kb < my_batches; ++kb)
+  {
+    const int batch = first + kb * warps_total;
+    const std::int32_t cell_next2 = kb + 2 < my_batches ? cell_of(batch + 2 * warps_total) : -1;
+    const T kappa_next = kb + 1 < my_batches ? kappa_of(batch + warps_total) : T(0);
+
+    // ---- geometry: Gc = kappa K K^T / det J from three edge vectors (lanes without a cell: unit cube)
+    T Gc[6];
+    {
+      T X[4][3];
+#pragma unroll
+      for (int v = 0; v < 4; ++v)
+      {
+        if (vid[v] >= 0)
+        {
+          const T* xk = xgeom + 3 * static_cast<std::int64_t>(vid[v]);
+          X[v][0] = __ldg(xk), X[v][1] = __ldg(xk + 1), X[v][2] = __ldg(xk + 2);
+        }
+        else
+        {
+          X[v][0] = T(v == 1), X[v][1] = T(v == 2), X[v][2] = T(v == 3);
+        }
+      }
+      T a[3], b[3], cc[3];
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+      {
+        a[i] = X[1][i] - X[0][i];
+        b[i] = X[2][i] - X[0][i];
+        cc[i] = X[3][i] - X[0][i];
+      }
+      otf_cell_g(a, b, cc, kappa, Gc); // order 00, 10, 20, 11, 21, 22
+    }
+    const T G00 = Gc[0], G01 = Gc[1], G02 = Gc[2], G11 = Gc[3], G12 = Gc[4], G22 = Gc[5];
+
+    // BC masking (reference :163-169): b[dof] = u[dof], the dof contributes 0 and receives nothing
+    if (cell_cur >= 0)
+    {
+#pragma unroll
+      for (int t = 0; t < ND2; ++t)
+        if (dof[t] < 0)
+        {
+          y[dof[t] & 0x7fffffff] = ul[t];
+          ul[t] = 0;
+        }
+    }
+    // next batch's indices: in flight during phase A
+    std::int32_t ndof[ND2];
+    load_dofs(cell_next, ndof);
+    load_vertex_ids(cell_next, vid);
+
+    // ---- phase A: y and z contractions of the plane, one output column k1 at a time.  Both loops below are real
+    // loops on purpose: unrolled, the 3 nd^2 table entries (more than the uniform register file holds in fp64)
+    // end up parked in ordinary registers next to 4 nd^2 accumulators and the kernel spills at 255 registers
+    // (first version: 30.6 GDoF/s at Q3, no better than the quadrature-space kernel).  Rolled, a column needs the
+    // plane, 4 nd z values and 8 sums; the table rows come from the constant bank by (uniform) dynamic index.
+#pragma unroll 1
+    for (int k1 = 0; k1 < ND; ++k1)
+    {
+      T mz[ND], sz[ND], cz[ND], ctz[ND]; // (M_z u, S_z u, C_z u, C^T_z u)[j][k1]
+#pragma unroll
+      for (int j = 0; j < ND; ++j)
+      {
+        T a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+        {
+          const T v = ul[j * ND + k];
+          a0 = fma(tab.M[k1 * ND + k], v, a0);
+          a1 = fma(tab.S[k1 * ND + k], v, a1);
+          a2 = fma(tab.C[k1 * ND + k], v, a2);
+          a3 = fma(tab.C[k * ND + k1], v, a3);
+        }
+        mz[j] = a0, sz[j] = a1, cz[j] = a2, ctz[j] = a3;
+      }
+#pragma unroll 1
+      for (int j1 = 0; j1 < ND; ++j1)
+      {
+        T p1 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0, s6 = 0, s7 = 0;
+#pragma unroll
+        for (int j = 0; j < ND; ++j)
+        {
+          const T Mj = tab.M[j1 * ND + j], Sj = tab.S[j1 * ND + j], Cj = tab.C[j1 * ND + j], Ctj = tab.C[j * ND + j1];
+          p1 = fma(Mj, mz[j], p1);                        // M_y M_z
+          s1 = fma(Sj, mz[j], s1);                        // S_y M_z
+          s2 = fma(Mj, sz[j], s2);                        // M_y S_z
+          s3 = fma(Cj, ctz[j], fma(Ctj, cz[j], s3));      // C_y C^T_z + C^T_y C_z
+          s4 = fma(Ctj, mz[j], s4);                       // C^T_y M_z
+          s5 = fma(Mj, ctz[j], s5);                       // M_y C^T_z
+          s6 = fma(Cj, mz[j], s6);                        // C_y M_z
+          s7 = fma(Mj, cz[j], s7);                        // M_y C_z
+        }
+        if (lane_ok)
+        {
+          T* dst = buf + k1 * SK + j1 * SJ + m * SI;
+          dst[0] = G00 * p1;                                 // for S_x
+          dst[PL] = fma(G11, s1, fma(G22, s2, G12 * s3));    // for M_x
+          dst[2 * PL] = fma(G01, s4, G02 * s5);              // for C_x
+          dst[3 * PL] = fma(G01, s6, G02 * s7);              // for C^T_x
+        }
+      }
+    }
+    __syncwarp();
+
+    // next batch's input values, and this lane's scatter indices (column (., j = m, .): a second look at the
+    // cell's row, which the team has just read): both in flight during phase B
+    T nul[ND2];
+    load_values(cell_next, ndof, nul);
+    std::int32_t sdof[ND2]; // [i1][k]
+    {
+      const std::int32_t* row = cell_cur >= 0 ? mdofmap + static_cast<std::int64_t>(cell_cur) * ND3 + m * ND : nullptr;
+#pragma unroll
+      for (int i1 = 0; i1 < ND; ++i1)
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+          sdof[i1 * ND + k] = row ? row[i1 * ND2 + k] : kBcBit;
+    }
+
+    // ---- phase B: x contraction for the column j = m (loop over the input plane i rolled, as above)
+    T out[ND2];
+#pragma unroll
+    for (int t = 0; t < ND2; ++t)
+      out[t] = 0;
+    if (lane_ok)
+    {
+#pragma unroll 1
+      for (int i = 0; i < ND; ++i)
+      {
+        T q1[ND], q2[ND], q3[ND], q4[ND];
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+        {
+          const T* src = buf + k * SK + m * SJ + i * SI;
+          q1[k] = src[0], q2[k] = src[PL], q3[k] = src[2 * PL], q4[k] = src[3 * PL];
+        }
+#pragma unroll
+        for (int i1 = 0; i1 < ND; ++i1)
+        {
+          const T Si = tab.S[i1 * ND + i], Mi = tab.M[i1 * ND + i], Ci = tab.C[i1 * ND + i], Cti = tab.C[i * ND + i1];
+#pragma unroll
+          for (int k = 0; k < ND; ++k)
+            out[i1 * ND + k] = fma(Si, q1[k], fma(Mi, q2[k], fma(Ci, q3[k], fma(Cti, q4[k], out[i1 * ND + k]))));
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < ND2; ++t)
+        if (sdof[t] >= 0)
+          atomicAdd(y + sdof[t], out[t]); // result unused -> RED.E.ADD (reference :424-425)
+    }
+    __syncwarp(); // the buffer is rewritten by the next batch's phase A
+
+#pragma unroll
+    for (int t = 0; t < ND2; ++t)
+    {
+      dof[t] = ndof[t];
+      ul[t] = nul[t];
+    }
+    cell_cur = cell_next;
+    cell_next = cell_next2;
+    kappa = kappa_next;
+  }
+}
+} // namespace bd

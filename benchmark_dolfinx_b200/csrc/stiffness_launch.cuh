@@ -7,6 +7,7 @@
 #include "stiffness_pencil.cuh"
 #include "stiffness_pencil_bulk.cuh"
 #include "stiffness_slab_otf.cuh"
+#include "stiffness_affine.cuh"
 
 namespace bd
 {
@@ -277,9 +278,78 @@ int launch_stiffness_slab_otf_cfg(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
+int affine_variant(); // TEMPORARY A/B: env BD_TMP_AFFINE (0 = off, otherwise MINB choice)
+
+// Dof-space kernel for meshes of parallelepipeds (stiffness_affine.cuh), degree <= 3.
+template <typename T, int P, int NQ, bool IDENTITY, int MINB>
+int launch_stiffness_affine(const StiffnessArgs& a)
+{
+  constexpr int ND = P + 1;
+  using AC = AffineConfig<T, P, 1>;
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d)
+    return fail(BD_ERR_INVALID_ARGUMENT, "the affine-cell kernel needs the masked dofmap, vertices and 1-D rule");
+  auto kernel = stiffness_affine_kernel<T, P, 1, MINB>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AC::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, AC::THREADS, AC::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  // 1-D matrices in double from the operator's own tables: Phi, DPhi = dphi1 * phi0 (or dphi1 when Phi = I)
+  SlabTables<T, ND, NQ> st;
+  fill_slab_tables<T, ND, NQ, IDENTITY>(st, a.phi0_host, a.dphi1_host);
+  AffineTables<T, ND> tab;
+  for (int r = 0; r < ND; ++r)
+    for (int c = 0; c < ND; ++c)
+    {
+      double m = 0, sv = 0, cv = 0;
+      for (int q = 0; q < NQ; ++q)
+      {
+        const double w = a.w1d[q];
+        const double pr = st.phi[q * ND + r], pc = st.phi[q * ND + c];
+        const double dr = st.dphi[q * ND + r], dc = st.dphi[q * ND + c];
+        m += w * pr * pc;
+        sv += w * dr * dc;
+        cv += w * dr * pc;
+      }
+      tab.M[r * ND + c] = static_cast<T>(m);
+      tab.S[r * ND + c] = static_cast<T>(sv);
+      tab.C[r * ND + c] = static_cast<T>(cv);
+    }
+  const std::int64_t nbatches = (a.ncells + AC::CW - 1) / AC::CW;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
+  kernel<<<grid, AC::THREADS, AC::CTA_SMEM, a.stream>>>(
+      static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.xgeom), a.gdofmap,
+      static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
 template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_slab_otf(const StiffnessArgs& a)
 {
+  if constexpr (P <= 3)
+  {
+    if (a.geom_mode == 1 && affine_variant() != 0)
+    {
+      if (affine_variant() == 2)
+        return launch_stiffness_affine<T, P, NQ, IDENTITY, 12>(a);
+      if (affine_variant() == 3)
+        return launch_stiffness_affine<T, P, NQ, IDENTITY, 16>(a);
+      return launch_stiffness_affine<T, P, NQ, IDENTITY, 1>(a);
+    }
+  }
   if constexpr (NQ > 6)
     return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");
   else
