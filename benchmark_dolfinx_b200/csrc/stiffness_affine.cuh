@@ -69,27 +69,29 @@ constexpr AffineStrides affine_strides(int nd, bool is_double)
   return {cw, nd * cw};
 }
 
-template <typename T, int P, int WARPS_>
+template <typename T, int P, int WARPS_, int KCH_>
 struct AffineConfig
 {
   static constexpr int ND = P + 1;
+  static constexpr int KCH = KCH_; // output columns k per exchange round (divides ND)
+  static_assert(ND % KCH_ == 0, "KCH must divide nd");
   static constexpr int CW = 32 / ND;
   static constexpr AffineStrides ST = affine_strides(ND, sizeof(T) == 8);
-  static constexpr int SI = ST.si, SJ = ST.sj, SK = ND * SJ, PL = ND * SK;
+  static constexpr int SI = ST.si, SJ = ST.sj, SK = ND * SJ, PL = KCH * SK;
   static constexpr int WARP_BYTES = (4 * PL * int(sizeof(T)) + 15) / 16 * 16;
   static constexpr int WARPS = WARPS_;
   static constexpr int THREADS = WARPS * 32;
   static constexpr int CTA_SMEM = WARPS * WARP_BYTES;
 };
 
-template <typename T, int P, int WARPS_, int MINB>
+template <typename T, int P, int WARPS_, int MINB, int KCH>
 __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     stiffness_affine_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ xgeom,
                             const std::int32_t* __restrict__ gdofmap, const T* __restrict__ cell_constants,
                             const std::int32_t* __restrict__ mdofmap, const std::int32_t* __restrict__ cells,
                             int ncells, const __grid_constant__ AffineTables<T, P + 1> tab)
 {
-  using AC = AffineConfig<T, P, WARPS_>;
+  using AC = AffineConfig<T, P, WARPS_, KCH>;
   constexpr int ND = AC::ND, CW = AC::CW, SI = AC::SI, SJ = AC::SJ, SK = AC::SK, PL = AC::PL;
   constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -127,15 +129,45 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
       v[t] = cell >= 0 ? u[d[t] & 0x7fffffff] : T(0);
   };
   // the four vertices that span a parallelepiped: v = 0, 4, 2, 1 of the tensor-product order
+  // (Loads of exactly the entries that are used: with 16-byte loads the unused components are dead registers, the
+  // compiler reuses them at once and the next instruction then waits for the load to land -- 15 % of the stall
+  // samples of the first version sat on such a write-after-write hazard.)
   auto load_vertex_ids = [&](std::int32_t cell, std::int32_t (&v)[4]) {
     if (cell >= 0)
     {
-      const int4* gd = reinterpret_cast<const int4*>(gdofmap + static_cast<std::int64_t>(cell) * 8);
-      const int4 lo = __ldg(gd), hi = __ldg(gd + 1);
-      v[0] = lo.x, v[1] = hi.x, v[2] = lo.z, v[3] = lo.y;
+      const std::int32_t* gd = gdofmap + static_cast<std::int64_t>(cell) * 8;
+      const int2 lo = __ldg(reinterpret_cast<const int2*>(gd));
+      v[0] = lo.x, v[3] = lo.y, v[2] = __ldg(gd + 2), v[1] = __ldg(gd + 4);
     }
     else
       v[0] = v[1] = v[2] = v[3] = -1;
+  };
+  auto load_vertices = [&](const std::int32_t (&v)[4], T (&X)[4][3]) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+      if (v[k] >= 0)
+      {
+        const T* xk = xgeom + 3 * static_cast<std::int64_t>(v[k]);
+        X[k][0] = __ldg(xk), X[k][1] = __ldg(xk + 1), X[k][2] = __ldg(xk + 2);
+      }
+      else
+      {
+        X[k][0] = T(k == 1), X[k][1] = T(k == 2), X[k][2] = T(k == 3); // lanes without a cell: unit cube
+      }
+    }
+  };
+  // Gc = kappa K K^T / det J from the three edge vectors, order 00, 10, 20, 11, 21, 22
+  auto cell_g = [&](const T (&X)[4][3], T kap, T (&G)[6]) {
+    T a[3], b[3], cc[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+    {
+      a[i] = X[1][i] - X[0][i];
+      b[i] = X[2][i] - X[0][i];
+      cc[i] = X[3][i] - X[0][i];
+    }
+    otf_cell_g(a, b, cc, kap, G);
   };
 
   std::int32_t dof[ND2], vid[4];
@@ -146,6 +178,12 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   load_vertex_ids(cell_cur, vid);
   load_dofs(cell_cur, dof);
   load_values(cell_cur, dof, ul);
+  T Gc[6]; // geometry of the current batch's cell, computed one batch ahead
+  {
+    T X[4][3];
+    load_vertices(vid, X);
+    cell_g(X, kappa, Gc);
+  }
 
   for (int kb = 0; kb < my_batches; ++kb)
   {
@@ -153,33 +191,6 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     const std::int32_t cell_next2 = kb + 2 < my_batches ? cell_of(batch + 2 * warps_total) : -1;
     const T kappa_next = kb + 1 < my_batches ? kappa_of(batch + warps_total) : T(0);
 
-    // ---- geometry: Gc = kappa K K^T / det J from three edge vectors (lanes without a cell: unit cube)
-    T Gc[6];
-    {
-      T X[4][3];
-#pragma unroll
-      for (int v = 0; v < 4; ++v)
-      {
-        if (vid[v] >= 0)
-        {
-          const T* xk = xgeom + 3 * static_cast<std::int64_t>(vid[v]);
-          X[v][0] = __ldg(xk), X[v][1] = __ldg(xk + 1), X[v][2] = __ldg(xk + 2);
-        }
-        else
-        {
-          X[v][0] = T(v == 1), X[v][1] = T(v == 2), X[v][2] = T(v == 3);
-        }
-      }
-      T a[3], b[3], cc[3];
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-      {
-        a[i] = X[1][i] - X[0][i];
-        b[i] = X[2][i] - X[0][i];
-        cc[i] = X[3][i] - X[0][i];
-      }
-      otf_cell_g(a, b, cc, kappa, Gc); // order 00, 10, 20, 11, 21, 22
-    }
     const T G00 = Gc[0], G01 = Gc[1], G02 = Gc[2], G11 = Gc[3], G12 = Gc[4], G22 = Gc[5];
 
     // BC masking (reference :163-169): b[dof] = u[dof], the dof contributes 0 and receives nothing
@@ -198,99 +209,119 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     load_dofs(cell_next, ndof);
     load_vertex_ids(cell_next, vid);
 
-    // ---- phase A: y and z contractions of the plane, one output column k1 at a time.  Both loops below are real
-    // loops on purpose: unrolled, the 3 nd^2 table entries (more than the uniform register file holds in fp64)
-    // end up parked in ordinary registers next to 4 nd^2 accumulators and the kernel spills at 255 registers
-    // (first version: 30.6 GDoF/s at Q3, no better than the quadrature-space kernel).  Rolled, a column needs the
-    // plane, 4 nd z values and 8 sums; the table rows come from the constant bank by (uniform) dynamic index.
-#pragma unroll 1
-    for (int k1 = 0; k1 < ND; ++k1)
-    {
-      T mz[ND], sz[ND], cz[ND], ctz[ND]; // (M_z u, S_z u, C_z u, C^T_z u)[j][k1]
-#pragma unroll
-      for (int j = 0; j < ND; ++j)
-      {
-        T a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-#pragma unroll
-        for (int k = 0; k < ND; ++k)
-        {
-          const T v = ul[j * ND + k];
-          a0 = fma(tab.M[k1 * ND + k], v, a0);
-          a1 = fma(tab.S[k1 * ND + k], v, a1);
-          a2 = fma(tab.C[k1 * ND + k], v, a2);
-          a3 = fma(tab.C[k * ND + k1], v, a3);
-        }
-        mz[j] = a0, sz[j] = a1, cz[j] = a2, ctz[j] = a3;
-      }
-#pragma unroll 1
-      for (int j1 = 0; j1 < ND; ++j1)
-      {
-        T p1 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0, s6 = 0, s7 = 0;
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
-        {
-          const T Mj = tab.M[j1 * ND + j], Sj = tab.S[j1 * ND + j], Cj = tab.C[j1 * ND + j], Ctj = tab.C[j * ND + j1];
-          p1 = fma(Mj, mz[j], p1);                        // M_y M_z
-          s1 = fma(Sj, mz[j], s1);                        // S_y M_z
-          s2 = fma(Mj, sz[j], s2);                        // M_y S_z
-          s3 = fma(Cj, ctz[j], fma(Ctj, cz[j], s3));      // C_y C^T_z + C^T_y C_z
-          s4 = fma(Ctj, mz[j], s4);                       // C^T_y M_z
-          s5 = fma(Mj, ctz[j], s5);                       // M_y C^T_z
-          s6 = fma(Cj, mz[j], s6);                        // C_y M_z
-          s7 = fma(Mj, cz[j], s7);                        // M_y C_z
-        }
-        if (lane_ok)
-        {
-          T* dst = buf + k1 * SK + j1 * SJ + m * SI;
-          dst[0] = G00 * p1;                                 // for S_x
-          dst[PL] = fma(G11, s1, fma(G22, s2, G12 * s3));    // for M_x
-          dst[2 * PL] = fma(G01, s4, G02 * s5);              // for C_x
-          dst[3 * PL] = fma(G01, s6, G02 * s7);              // for C^T_x
-        }
-      }
-    }
-    __syncwarp();
-
-    // next batch's input values, and this lane's scatter indices (column (., j = m, .): a second look at the
-    // cell's row, which the team has just read): both in flight during phase B
-    T nul[ND2];
-    load_values(cell_next, ndof, nul);
-    std::int32_t sdof[ND2]; // [i1][k]
-    {
-      const std::int32_t* row = cell_cur >= 0 ? mdofmap + static_cast<std::int64_t>(cell_cur) * ND3 + m * ND : nullptr;
-#pragma unroll
-      for (int i1 = 0; i1 < ND; ++i1)
-#pragma unroll
-        for (int k = 0; k < ND; ++k)
-          sdof[i1 * ND + k] = row ? row[i1 * ND2 + k] : kBcBit;
-    }
-
-    // ---- phase B: x contraction for the column j = m (loop over the input plane i rolled, as above)
+    // ---- The two phases, in rounds of KCH output columns k (k is a spectator of the x contraction, so the exchange
+    // buffer only ever holds KCH columns: 4 planes x KCH x nd^2 values per cell instead of 4 nd^3, which is what
+    // lets 16 one-warp CTAs share an SM).
+    //
+    // Phase A (y and z contractions of the plane, one output column k1 at a time).  The loops over j1 and, for
+    // KCH > 1, k1 are real loops on purpose: unrolled, the 3 nd^2 table entries (more than the uniform register
+    // file holds in fp64) end up parked in ordinary registers next to 4 nd^2 accumulators and the kernel spills at
+    // 255 registers (first version: 30.6 GDoF/s at Q3, no better than the quadrature-space kernel).  Rolled, a
+    // column needs the plane, 4 nd z values and 8 sums; table rows come from the constant bank by dynamic index.
     T out[ND2];
 #pragma unroll
     for (int t = 0; t < ND2; ++t)
       out[t] = 0;
-    if (lane_ok)
+    T nul[ND2];
+    T Xn[4][3];             // next batch's vertices, requested with nul
+    std::int32_t sdof[ND2]; // scatter indices of phase B, [i1][k]
+#pragma unroll
+    for (int r = 0; r < ND / KCH; ++r)
     {
+      if (r > 0)
+        __syncwarp(); // the previous round's phase B is done with the buffer
 #pragma unroll 1
-      for (int i = 0; i < ND; ++i)
+      for (int kk = 0; kk < KCH; ++kk)
       {
-        T q1[ND], q2[ND], q3[ND], q4[ND];
+        const int k1 = r * KCH + kk;
+        T mz[ND], sz[ND], cz[ND], ctz[ND]; // (M_z u, S_z u, C_z u, C^T_z u)[j][k1]
 #pragma unroll
-        for (int k = 0; k < ND; ++k)
+        for (int j = 0; j < ND; ++j)
         {
-          const T* src = buf + k * SK + m * SJ + i * SI;
-          q1[k] = src[0], q2[k] = src[PL], q3[k] = src[2 * PL], q4[k] = src[3 * PL];
-        }
-#pragma unroll
-        for (int i1 = 0; i1 < ND; ++i1)
-        {
-          const T Si = tab.S[i1 * ND + i], Mi = tab.M[i1 * ND + i], Ci = tab.C[i1 * ND + i], Cti = tab.C[i * ND + i1];
+          T a0 = 0, a1 = 0, a2 = 0, a3 = 0;
 #pragma unroll
           for (int k = 0; k < ND; ++k)
-            out[i1 * ND + k] = fma(Si, q1[k], fma(Mi, q2[k], fma(Ci, q3[k], fma(Cti, q4[k], out[i1 * ND + k]))));
+          {
+            const T v = ul[j * ND + k];
+            a0 = fma(tab.M[k1 * ND + k], v, a0);
+            a1 = fma(tab.S[k1 * ND + k], v, a1);
+            a2 = fma(tab.C[k1 * ND + k], v, a2);
+            a3 = fma(tab.C[k * ND + k1], v, a3);
+          }
+          mz[j] = a0, sz[j] = a1, cz[j] = a2, ctz[j] = a3;
+        }
+#pragma unroll 1
+        for (int j1 = 0; j1 < ND; ++j1)
+        {
+          T p1 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0, s6 = 0, s7 = 0;
+#pragma unroll
+          for (int j = 0; j < ND; ++j)
+          {
+            const T Mj = tab.M[j1 * ND + j], Sj = tab.S[j1 * ND + j], Cj = tab.C[j1 * ND + j], Ctj = tab.C[j * ND + j1];
+            p1 = fma(Mj, mz[j], p1);                   // M_y M_z
+            s1 = fma(Sj, mz[j], s1);                   // S_y M_z
+            s2 = fma(Mj, sz[j], s2);                   // M_y S_z
+            s3 = fma(Cj, ctz[j], fma(Ctj, cz[j], s3)); // C_y C^T_z + C^T_y C_z
+            s4 = fma(Ctj, mz[j], s4);                  // C^T_y M_z
+            s5 = fma(Mj, ctz[j], s5);                  // M_y C^T_z
+            s6 = fma(Cj, mz[j], s6);                   // C_y M_z
+            s7 = fma(Mj, cz[j], s7);                   // M_y C_z
+          }
+          if (lane_ok)
+          {
+            T* dst = buf + kk * SK + j1 * SJ + m * SI;
+            dst[0] = G00 * p1;                              // for S_x
+            dst[PL] = fma(G11, s1, fma(G22, s2, G12 * s3)); // for M_x
+            dst[2 * PL] = fma(G01, s4, G02 * s5);           // for C_x
+            dst[3 * PL] = fma(G01, s6, G02 * s7);           // for C^T_x
+          }
         }
       }
+      __syncwarp();
+
+      if (r == 0)
+      {
+        // next batch's input values, and this lane's scatter indices (column (., j = m, .): a second look at the
+        // cell's row, which the team has just read): in flight during phase B
+        load_values(cell_next, ndof, nul);
+        load_vertices(vid, Xn); // vid already holds the next batch's vertex ids
+        const std::int32_t* row = cell_cur >= 0 ? mdofmap + static_cast<std::int64_t>(cell_cur) * ND3 + m * ND : nullptr;
+#pragma unroll
+        for (int i1 = 0; i1 < ND; ++i1)
+#pragma unroll
+          for (int k = 0; k < ND; ++k)
+            sdof[i1 * ND + k] = row ? row[i1 * ND2 + k] : kBcBit;
+      }
+
+      // Phase B: x contraction for the column j = m and the round's k columns (loop over the input plane i rolled)
+      if (lane_ok)
+      {
+#pragma unroll 1
+        for (int i = 0; i < ND; ++i)
+        {
+          T q1[KCH], q2[KCH], q3[KCH], q4[KCH];
+#pragma unroll
+          for (int kk = 0; kk < KCH; ++kk)
+          {
+            const T* src = buf + kk * SK + m * SJ + i * SI;
+            q1[kk] = src[0], q2[kk] = src[PL], q3[kk] = src[2 * PL], q4[kk] = src[3 * PL];
+          }
+#pragma unroll
+          for (int i1 = 0; i1 < ND; ++i1)
+          {
+            const T Si = tab.S[i1 * ND + i], Mi = tab.M[i1 * ND + i], Ci = tab.C[i1 * ND + i], Cti = tab.C[i * ND + i1];
+#pragma unroll
+            for (int kk = 0; kk < KCH; ++kk)
+            {
+              T& o = out[i1 * ND + r * KCH + kk];
+              o = fma(Si, q1[kk], fma(Mi, q2[kk], fma(Ci, q3[kk], fma(Cti, q4[kk], o))));
+            }
+          }
+        }
+      }
+    }
+    if (lane_ok)
+    {
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
         if (sdof[t] >= 0)
@@ -307,6 +338,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     cell_cur = cell_next;
     cell_next = cell_next2;
     kappa = kappa_next;
+    cell_g(Xn, kappa, Gc);
   }
 }
 } // namespace bd

@@ -281,18 +281,18 @@ int launch_stiffness_slab_otf_cfg(const StiffnessArgs& a)
 int affine_variant(); // TEMPORARY A/B: env BD_TMP_AFFINE (0 = off, otherwise MINB choice)
 
 // Dof-space kernel for meshes of parallelepipeds (stiffness_affine.cuh), degree <= 3.
-template <typename T, int P, int NQ, bool IDENTITY, int MINB>
+template <typename T, int P, int NQ, bool IDENTITY, int MINB, int KCH>
 int launch_stiffness_affine(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
-  using AC = AffineConfig<T, P, 1>;
+  using AC = AffineConfig<T, P, 1, KCH>;
   if (a.ncells == 0)
     return BD_SUCCESS;
   if (a.ncells > 0x7fffffffLL)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d)
     return fail(BD_ERR_INVALID_ARGUMENT, "the affine-cell kernel needs the masked dofmap, vertices and 1-D rule");
-  auto kernel = stiffness_affine_kernel<T, P, 1, MINB>;
+  auto kernel = stiffness_affine_kernel<T, P, 1, MINB, KCH>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -343,11 +343,17 @@ int launch_stiffness_slab_otf(const StiffnessArgs& a)
   {
     if (a.geom_mode == 1 && affine_variant() != 0)
     {
+      constexpr int ND = P + 1;
+      constexpr int HALF = (ND % 2 == 0) ? ND / 2 : 1;
       if (affine_variant() == 2)
-        return launch_stiffness_affine<T, P, NQ, IDENTITY, 12>(a);
+        return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, HALF>(a);
       if (affine_variant() == 3)
-        return launch_stiffness_affine<T, P, NQ, IDENTITY, 16>(a);
-      return launch_stiffness_affine<T, P, NQ, IDENTITY, 1>(a);
+        return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, 1>(a);
+      if (affine_variant() == 4)
+        return launch_stiffness_affine<T, P, NQ, IDENTITY, 16, HALF>(a);
+      if (affine_variant() == 5)
+        return launch_stiffness_affine<T, P, NQ, IDENTITY, 16, 1>(a);
+      return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, ND>(a);
     }
   }
   if constexpr (NQ > 6)

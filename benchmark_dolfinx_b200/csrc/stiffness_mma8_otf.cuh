@@ -115,14 +115,17 @@ __global__ void __launch_bounds__(kMma8Warps * 32, MINB)
   };
   constexpr int NV = AFFINE_ONLY ? 4 : 8;
   auto load_vertex_ids = [&](std::int32_t cell, std::int32_t (&v)[NV]) {
-    const int4* gd = reinterpret_cast<const int4*>(gdofmap + static_cast<std::int64_t>(cell) * 8);
-    const int4 lo = __ldg(gd), hi = __ldg(gd + 1);
     if constexpr (AFFINE_ONLY)
     {
-      v[0] = lo.x, v[1] = hi.x, v[2] = lo.z, v[3] = lo.y; // vertices 0, 4, 2, 1
+      // vertices 0, 4, 2, 1 with loads of exactly those entries (see stiffness_slab_otf.cuh)
+      const std::int32_t* gd = gdofmap + static_cast<std::int64_t>(cell) * 8;
+      const int2 lo = __ldg(reinterpret_cast<const int2*>(gd));
+      v[0] = lo.x, v[3] = lo.y, v[2] = __ldg(gd + 2), v[1] = __ldg(gd + 4);
     }
     else
     {
+      const int4* gd = reinterpret_cast<const int4*>(gdofmap + static_cast<std::int64_t>(cell) * 8);
+      const int4 lo = __ldg(gd), hi = __ldg(gd + 1);
       v[0] = lo.x, v[1] = lo.y, v[2] = lo.z, v[3] = lo.w;
       v[4] = hi.x, v[5] = hi.y, v[6] = hi.z, v[7] = hi.w;
     }

@@ -307,17 +307,22 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   auto load_vertex_ids = [&](std::int32_t cell, std::int32_t (&v)[NV]) {
     if (cell >= 0)
     {
-      const int4* gd = reinterpret_cast<const int4*>(gdofmap + static_cast<std::int64_t>(cell) * 8);
-      const int4 lo = __ldg(gd), hi = __ldg(gd + 1);
       if constexpr (AFFINE_ONLY)
       {
+        // exactly the four entries that are used: the unused components of a 16-byte load are dead registers,
+        // the compiler reuses them at once and the next instruction then waits for the load to land (ncu: 8 % of
+        // the stall samples of the first version sat on that write-after-write hazard)
+        const std::int32_t* gd = gdofmap + static_cast<std::int64_t>(cell) * 8;
+        const int2 lo = __ldg(reinterpret_cast<const int2*>(gd));
         v[0] = lo.x;
-        v[1] = hi.x;
-        v[2] = lo.z;
         v[3] = lo.y;
+        v[2] = __ldg(gd + 2);
+        v[1] = __ldg(gd + 4);
       }
       else
       {
+        const int4* gd = reinterpret_cast<const int4*>(gdofmap + static_cast<std::int64_t>(cell) * 8);
+        const int4 lo = __ldg(gd), hi = __ldg(gd + 1);
         v[0] = lo.x, v[1] = lo.y, v[2] = lo.z, v[3] = lo.w;
         v[4] = hi.x, v[5] = hi.y, v[6] = hi.z, v[7] = hi.w;
       }
