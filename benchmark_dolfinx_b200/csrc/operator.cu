@@ -376,7 +376,9 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
   if (op->geom_mode != 0)
   {
     kernel = op->nq >= 7 ? "bd::stiffness_mma8_otf_kernel (fp64 DMMA m8n8k4 arithmetic, geometry on the fly)"
-                         : "bd::stiffness_slab_otf_kernel (register slabs, geometry on the fly)";
+             : (op->geom_mode == 1 && affine_kernel_used(op->scalar_bits, op->degree, op->is_identity))
+                 ? "bd::stiffness_affine_kernel (dof-space 1-D operators M, S, C; geometry on the fly)"
+                 : "bd::stiffness_slab_otf_kernel (register slabs, geometry on the fly)";
     snprintf(buf, n, "%s, T=%s, P=%d, nq=%d, %s", kernel, t, op->degree, op->nq,
              op->geom_mode == 1 ? "all cells affine: G(q) = w_q G_cell" : "general cells: J(q) from the 8 vertices");
     return BD_SUCCESS;

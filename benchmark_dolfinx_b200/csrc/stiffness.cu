@@ -48,15 +48,6 @@ int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::i
   return BD_SUCCESS;
 }
 
-int affine_variant()
-{
-  static const int v = [] {
-    const char* e = std::getenv("BD_TMP_AFFINE");
-    return e ? std::atoi(e) : 1;
-  }();
-  return v;
-}
-
 int preferred_g_layout(int scalar_bits, int degree, int nq)
 {
   // pencil kernel (reference layout): see pencil_instantiated() in stiffness_launch.cuh

@@ -278,7 +278,15 @@ int launch_stiffness_slab_otf_cfg(const StiffnessArgs& a)
   return BD_SUCCESS;
 }
 
-int affine_variant(); // TEMPORARY A/B: env BD_TMP_AFFINE (0 = off, otherwise MINB choice)
+// Where the dof-space kernel (stiffness_affine.cuh) replaces the quadrature-space on-the-fly kernel on meshes of
+// parallelepipeds (measured on one B200, profiles/r2_affine_ab.txt): qmode 1 with degree <= 3 (Q3 fp64 44.7 vs 32.0
+// GDoF/s, Q2 34.2 vs 24.3, Q1 14.7 vs 8.0, Q3 fp32 74.1 vs 46.9) and degree 4 in fp32 (70.0 vs 56.6).  Not at
+// qmode 0, where Phi = I makes the quadrature-space kernel the cheaper one (Q3 59.9 vs 41.4, Q2 49.2 vs 34.2,
+// Q1 19.3 vs 14.7), and not at degree 4 in fp64 (24.3 vs 32.1: its exchange buffer leaves 3 warps per SM).
+constexpr bool affine_kernel_used(int scalar_bits, int degree, bool identity)
+{
+  return !identity && (degree <= 3 || (degree == 4 && scalar_bits == 32));
+}
 
 // Dof-space kernel for meshes of parallelepipeds (stiffness_affine.cuh), degree <= 3.
 template <typename T, int P, int NQ, bool IDENTITY, int MINB, int KCH>
@@ -339,22 +347,12 @@ int launch_stiffness_affine(const StiffnessArgs& a)
 template <typename T, int P, int NQ, bool IDENTITY>
 int launch_stiffness_slab_otf(const StiffnessArgs& a)
 {
-  if constexpr (P <= 3)
+  if constexpr (affine_kernel_used(int(sizeof(T)) * 8, P, IDENTITY))
   {
-    if (a.geom_mode == 1 && affine_variant() != 0)
-    {
-      constexpr int ND = P + 1;
-      constexpr int HALF = (ND % 2 == 0) ? ND / 2 : 1;
-      if (affine_variant() == 2)
-        return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, HALF>(a);
-      if (affine_variant() == 3)
-        return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, 1>(a);
-      if (affine_variant() == 4)
-        return launch_stiffness_affine<T, P, NQ, IDENTITY, 16, HALF>(a);
-      if (affine_variant() == 5)
-        return launch_stiffness_affine<T, P, NQ, IDENTITY, 16, 1>(a);
-      return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, ND>(a);
-    }
+    // every cell a parallelepiped: the dof-space kernel (one exchange round, uncapped registers: measured best,
+    // profiles/r2_affine_ab.txt)
+    if (a.geom_mode == 1)
+      return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, P + 1>(a);
   }
   if constexpr (NQ > 6)
     return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");
