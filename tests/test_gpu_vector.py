@@ -86,3 +86,10 @@ def test_set_value_pack_unpack(dtype):
     ref = np.zeros(n, dtype=dtype)
     ref[idx] = v[idx]                                              # out[idx[i]] = in[i]
     assert np.array_equal(out.cpu().numpy(), ref)
+
+
+def test_fp64_peak_measurement():
+    """bd_fp64_peak (roofline denominators of bench.py): plausible numbers for a B200-class device."""
+    import benchmark_dolfinx_b200 as bd
+    dfma, dmma = bd.fp64_peak()
+    assert 5.0 < dfma < 100.0 and 5.0 < dmma < 100.0
