@@ -34,39 +34,60 @@ struct AffineTables
 
 struct AffineStrides
 {
-  int si, sj;
+  int ch, si, sj; // cells per group of the cell index, strides of i and j
 };
 
-// Strides of the exchange buffer, element (plane p, i, j, k, cell c) at p*PL + k*sk + j*sj + i*si + c:
-// phase A writes with lanes (c, i) [fixed p, j, k], phase B reads with lanes (c, j) [fixed p, i, k]; both must be
-// bank-conflict free within each group of lanes the hardware serves together (16 for 8-byte, 32 for 4-byte words).
-constexpr AffineStrides affine_strides(int nd, bool is_double)
+// Layout of the exchange buffer.  Element (plane p, i, j, k, cell c) sits at
+//     p*PL + (c / CH)*HS + k*SK + j*SJ + i*SI + (c % CH),      SK = nd*SJ, HS = KCH*SK, PL = ceil(CW / CH)*HS.
+// Phase A writes with lanes (c, i) [fixed p, j, k], phase B reads with lanes (c, j) [fixed p, i, k]; both must be
+// bank-conflict free within each group of lanes the hardware serves together (16 lanes for 8-byte words, 32 for
+// 4-byte words).  With CH = CW the cell index is simply the fastest one; splitting it (CH = cells per 16-lane group)
+// needs less padding when the groups coincide with whole cells (nd = 4 in fp64: 20.5 KB per warp instead of 26).
+constexpr bool affine_strides_ok(int nd, bool is_double, int ch, int si, int sj)
 {
   const int cw = 32 / nd;
   const int nbanks = is_double ? 16 : 32, group = is_double ? 16 : 32;
-  for (int si = cw; si < cw + 33; ++si)
-    for (int sj = nd * si; sj < nd * si + 33; ++sj)
+  const int hs = nd * nd * sj; // any multiple of the bank count in effect: only (c / ch) * hs mod nbanks matters
+  for (int pass = 0; pass < 2; ++pass)
+    for (int g0 = 0; g0 < 32; g0 += group)
     {
-      bool ok = true;
-      for (int pass = 0; pass < 2 && ok; ++pass)
-        for (int g0 = 0; g0 < 32 && ok; g0 += group)
-        {
-          bool used[32] = {};
-          for (int l = g0; l < g0 + group && ok; ++l)
-          {
-            const int c = l / nd, m = l % nd;
-            if (c >= cw)
-              continue;
-            const int b = (m * (pass == 0 ? si : sj) + c) % nbanks;
-            if (used[b])
-              ok = false;
-            used[b] = true;
-          }
-        }
-      if (ok)
-        return {si, sj};
+      bool used[32] = {};
+      for (int l = g0; l < g0 + group; ++l)
+      {
+        const int c = l / nd, m = l % nd;
+        if (c >= cw)
+          continue;
+        const int b = ((c / ch) * hs + m * (pass == 0 ? si : sj) + (c % ch)) % nbanks;
+        if (used[b])
+          return false;
+        used[b] = true;
+      }
     }
-  return {cw, nd * cw};
+  return true;
+}
+constexpr AffineStrides affine_strides(int nd, bool is_double)
+{
+  const int cw = 32 / nd;
+  AffineStrides best{cw, cw, nd * cw};
+  int best_size = 1 << 30;
+  for (int ch = 1; ch <= cw; ++ch)
+  {
+    if (cw % ch != 0)
+      continue;
+    for (int si = ch; si < ch + 33; ++si)
+      for (int sj = nd * si; sj < nd * si + 33; ++sj)
+        if (affine_strides_ok(nd, is_double, ch, si, sj))
+        {
+          const int size = (cw / ch) * nd * nd * sj;
+          if (size < best_size)
+          {
+            best_size = size;
+            best = AffineStrides{ch, si, sj};
+          }
+          break; // larger sj only grows the buffer for this (ch, si)
+        }
+  }
+  return best;
 }
 
 template <typename T, int P, int WARPS_, int KCH_>
@@ -77,7 +98,7 @@ struct AffineConfig
   static_assert(ND % KCH_ == 0, "KCH must divide nd");
   static constexpr int CW = 32 / ND;
   static constexpr AffineStrides ST = affine_strides(ND, sizeof(T) == 8);
-  static constexpr int SI = ST.si, SJ = ST.sj, SK = ND * SJ, PL = KCH * SK;
+  static constexpr int CH = ST.ch, SI = ST.si, SJ = ST.sj, SK = ND * SJ, HS = KCH * SK, PL = (CW / CH) * HS;
   static constexpr int WARP_BYTES = (4 * PL * int(sizeof(T)) + 15) / 16 * 16;
   static constexpr int WARPS = WARPS_;
   static constexpr int THREADS = WARPS * 32;
@@ -94,6 +115,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   using AC = AffineConfig<T, P, WARPS_, KCH>;
   constexpr int ND = AC::ND, CW = AC::CW, SI = AC::SI, SJ = AC::SJ, SK = AC::SK, PL = AC::PL;
   constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
+  constexpr bool DEEP = sizeof(T) == 8;
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;
@@ -101,7 +123,8 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   const int c = lane / ND;
   const int m = lane - c * ND;
   const bool lane_ok = c < CW;
-  T* buf = reinterpret_cast<T*>(smem_raw + warp * AC::WARP_BYTES) + (lane_ok ? c : 0);
+  T* buf = reinterpret_cast<T*>(smem_raw + warp * AC::WARP_BYTES)
+           + (lane_ok ? (c / AC::CH) * AC::HS + (c % AC::CH) : 0);
 
   const int nbatches = (ncells + CW - 1) / CW;
   const int warps_total = gridDim.x * AC::WARPS;
@@ -170,13 +193,18 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     otf_cell_g(a, b, cc, kap, G);
   };
 
-  std::int32_t dof[ND2], vid[4];
+  // Software pipeline over the warp's batches: dof and vertex indices are requested two batches ahead, input values
+  // and vertex coordinates one batch ahead (at the top of the batch, so that they have the whole batch to arrive:
+  // requested after phase A, as in the first version, 15 % of the stall samples sat on their first use).
+  std::int32_t dof[ND2], ndof[ND2], vid[4];
   T ul[ND2];
   std::int32_t cell_cur = my_batches > 0 ? cell_of(first) : -1;
   std::int32_t cell_next = my_batches > 1 ? cell_of(first + warps_total) : -1;
   T kappa = my_batches > 0 ? kappa_of(first) : T(0);
   load_vertex_ids(cell_cur, vid);
   load_dofs(cell_cur, dof);
+  if constexpr (DEEP)
+    load_dofs(cell_next, ndof);
   load_values(cell_cur, dof, ul);
   T Gc[6]; // geometry of the current batch's cell, computed one batch ahead
   {
@@ -184,6 +212,8 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     load_vertices(vid, X);
     cell_g(X, kappa, Gc);
   }
+  if constexpr (DEEP)
+    load_vertex_ids(cell_next, vid);
 
   for (int kb = 0; kb < my_batches; ++kb)
   {
@@ -204,10 +234,25 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
           ul[t] = 0;
         }
     }
-    // next batch's indices: in flight during phase A
-    std::int32_t ndof[ND2];
-    load_dofs(cell_next, ndof);
-    load_vertex_ids(cell_next, vid);
+    // next batch's input values and vertices (their indices arrived during the previous batch), and the indices of
+    // the batch after it
+    // (DEEP = fp64.  In fp32 the extra index set costs more than the earlier request gains -- Q4 fp32 70.2 vs 58.8
+    // GDoF/s -- so there the values and vertices are requested after phase A and the indices one batch ahead.)
+    T nul[ND2];
+    T Xn[4][3];
+    std::int32_t n2dof[DEEP ? ND2 : 1];
+    if constexpr (DEEP)
+    {
+      load_values(cell_next, ndof, nul);
+      load_vertices(vid, Xn);
+      load_dofs(cell_next2, n2dof);
+      load_vertex_ids(cell_next2, vid);
+    }
+    else
+    {
+      load_dofs(cell_next, ndof);
+      load_vertex_ids(cell_next, vid);
+    }
 
     // ---- The two phases, in rounds of KCH output columns k (k is a spectator of the x contraction, so the exchange
     // buffer only ever holds KCH columns: 4 planes x KCH x nd^2 values per cell instead of 4 nd^3, which is what
@@ -222,8 +267,6 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
 #pragma unroll
     for (int t = 0; t < ND2; ++t)
       out[t] = 0;
-    T nul[ND2];
-    T Xn[4][3];             // next batch's vertices, requested with nul
     std::int32_t sdof[ND2]; // scatter indices of phase B, [i1][k]
 #pragma unroll
     for (int r = 0; r < ND / KCH; ++r)
@@ -281,10 +324,13 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
 
       if (r == 0)
       {
-        // next batch's input values, and this lane's scatter indices (column (., j = m, .): a second look at the
-        // cell's row, which the team has just read): in flight during phase B
-        load_values(cell_next, ndof, nul);
-        load_vertices(vid, Xn); // vid already holds the next batch's vertex ids
+        // this lane's scatter indices (column (., j = m, .): a second look at the cell's row, which the team has
+        // just read): in flight during phase B
+        if constexpr (!DEEP)
+        {
+          load_values(cell_next, ndof, nul);
+          load_vertices(vid, Xn);
+        }
         const std::int32_t* row = cell_cur >= 0 ? mdofmap + static_cast<std::int64_t>(cell_cur) * ND3 + m * ND : nullptr;
 #pragma unroll
         for (int i1 = 0; i1 < ND; ++i1)
@@ -325,7 +371,11 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
         if (sdof[t] >= 0)
+#ifdef BD_AFFINE_NOATOMIC
+          y[sdof[t]] = out[t]; // TIMING EXPERIMENT ONLY (wrong results)
+#else
           atomicAdd(y + sdof[t], out[t]); // result unused -> RED.E.ADD (reference :424-425)
+#endif
     }
     __syncwarp(); // the buffer is rewritten by the next batch's phase A
 
@@ -333,6 +383,8 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     for (int t = 0; t < ND2; ++t)
     {
       dof[t] = ndof[t];
+      if constexpr (DEEP)
+        ndof[t] = n2dof[t];
       ul[t] = nul[t];
     }
     cell_cur = cell_next;
