@@ -303,6 +303,35 @@ def reference_gpu_kernel_leg(bd, degree, qmode, dtype, ndofs, steps):
     return out
 
 
+def bind_to_gpu_numa_node(device_index):
+    """Run this rank on the host cores next to its GPU (the NUMA node the GPU's PCIe root hangs off), BEFORE any
+    pinned host memory is allocated: pinned pages are placed on the node of the allocating thread, and with every
+    rank on node 0 the H2D/D2H copies of 8 GPUs share one socket's memory controllers and the inter-socket link
+    (round 1: 43 GB/s per GPU each way at N = 1, 8 GB/s at N = 8).  Returns a description for the JSON line."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device_index)
+        bdf = f"{getattr(pr, 'pci_domain_id', 0):04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return {"pci": bdf, "numa_node": node, "bound": False, "why": "no NUMA information for the device"}
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpulist = f.read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if not use:
+            return {"pci": bdf, "numa_node": node, "bound": False, "why": "node's cores are outside this process's cpuset"}
+        os.sched_setaffinity(0, use)
+        return {"pci": bdf, "numa_node": node, "bound": True, "cores": len(use)}
+    except Exception as exc:
+        return {"bound": False, "why": f"{type(exc).__name__}: {exc}"}
+
+
 # ----------------------------------------------------------------------------- our arm
 FP64_PEAKS = None   # (DFMA, DMMA) TFLOP/s measured by bd_fp64_peak at the start of the run
 
@@ -602,6 +631,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_numa_node(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -736,7 +766,7 @@ def main():
             "vs_baseline": None, "dtype": f"f{args.float}", "data": "synthetic", "config": cfg,
             "roofline": head["roofline"], "cpu_baseline": cpu, "gpu_qmode0": gpu_q0, "e2e": e2e, "cg": cg,
             "halo": head["halo"], "variants": variants, "q6": q6, "parity": parity, "reference_gpu_kernel": ref_gpu,
-            "fp64_peaks_measured_tflops": {"dfma": FP64_PEAKS[0], "dmma": FP64_PEAKS[1]},
+            "host_binding_rank0": numa, "fp64_peaks_measured_tflops": {"dfma": FP64_PEAKS[0], "dmma": FP64_PEAKS[1]},
             "gpu_launches": gpu_launches, "clocks": head["clocks"], "u_norm": unorm, "y_norm": ynorm,
         }
         print(json.dumps(line), flush=True)
