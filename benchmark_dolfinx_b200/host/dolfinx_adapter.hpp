@@ -2,10 +2,12 @@
 // benchdolfinx_b200 C ABI.  Meant to be dropped next to the reference's sources and included in
 // place of its laplacian.hpp GPU class (src/laplacian.hpp:89-447) and cg.hpp (src/cg.hpp:89-169).
 //
-// STATUS: DOLFINx, Basix and MPI are not installable in the build environment of this repository,
-// so this header has only been compiled against the API mock-ups under tests/mock_dolfinx/
-// (tests/test_adapter_compiles.py) and never run.  Everything it calls in the C ABI is exercised
-// by the stand-in path (host/*.hpp, tests/).
+// STATUS: DOLFINx, Basix and MPI are not installable in the build environment of this repository.  The header is
+// (a) type-checked against declaration-only mock-ups (tests/mock_dolfinx/, tests/test_adapter_compiles.py) and
+// (b) EXECUTED on the GPU against functional stand-ins (tests/mock_dolfinx/functional/: DOLFINx classes backed by the
+// structured stand-in mesh, Basix calls backed by bd_tables, MPI as threads-as-ranks): constructor, halo lists,
+// apply and cg_solve reproduce the reference's known answers (tests/test_gpu_adapter.py).  It has not met the real
+// libraries.
 //
 // What it does, in the reference's terms:
 //   * constructor  = src/laplacian.hpp:102-227: lcells/bcells (compute_boundary_cells), BC markers,
@@ -50,6 +52,69 @@ inline void check(int rc)
     throw std::runtime_error(bd_last_error());
 }
 
+/// What every owner sends to whom, and where received entries land: the host-side part of the forward-scatter plan
+/// (what dolfinx::common::Scatterer derives from an IndexMap), separated from the NCCL objects so that it can be
+/// checked on its own.
+struct HaloLists
+{
+  std::vector<std::int32_t> send_ranks, recv_ranks; ///< neighbour ranks, ascending
+  std::vector<std::int64_t> send_counts, recv_counts;
+  std::vector<std::int32_t> send_idx; ///< local (owned) indices to send, concatenated by destination rank
+  std::vector<std::int32_t> order;    ///< message entry i (receives concatenated by source rank) lands at ghost order[i]
+  bool ordered = true;                ///< order is the identity: receives can land in the ghost segment directly
+};
+
+/// One MPI_Alltoall + one MPI_Alltoallv: every rank tells the owners of its ghosts which global indices it wants.
+inline HaloLists compute_halo_lists(const dolfinx::common::IndexMap& map)
+{
+  MPI_Comm comm = map.comm();
+  int size = 1;
+  MPI_Comm_size(comm, &size);
+  HaloLists L;
+  const std::int64_t offset = map.local_range()[0];
+  std::span<const std::int64_t> ghosts = map.ghosts();
+  std::span<const int> owners = map.owners();
+  const std::size_t ng = ghosts.size();
+  // message order: ghosts grouped by owner rank (stable), position i of the messages is ghost order[i]
+  L.order.resize(ng);
+  std::iota(L.order.begin(), L.order.end(), 0);
+  std::stable_sort(L.order.begin(), L.order.end(), [&](int a, int b) { return owners[a] < owners[b]; });
+  L.ordered = std::is_sorted(L.order.begin(), L.order.end());
+  std::vector<int> want_count(size, 0);
+  for (std::size_t i = 0; i < ng; ++i)
+    ++want_count[owners[i]];
+  std::vector<int> want_displ(size + 1, 0);
+  std::partial_sum(want_count.begin(), want_count.end(), want_displ.begin() + 1);
+  std::vector<std::int64_t> want(ng);
+  for (std::size_t i = 0; i < ng; ++i)
+    want[i] = ghosts[L.order[i]];
+  // owners learn what to send
+  std::vector<int> give_count(size, 0);
+  MPI_Alltoall(want_count.data(), 1, MPI_INT, give_count.data(), 1, MPI_INT, comm);
+  std::vector<int> give_displ(size + 1, 0);
+  std::partial_sum(give_count.begin(), give_count.end(), give_displ.begin() + 1);
+  std::vector<std::int64_t> give(give_displ[size]);
+  MPI_Alltoallv(want.data(), want_count.data(), want_displ.data(), MPI_INT64_T, give.data(), give_count.data(),
+                give_displ.data(), MPI_INT64_T, comm);
+  for (int r = 0; r < size; ++r)
+  {
+    if (give_count[r] > 0)
+    {
+      L.send_ranks.push_back(r);
+      L.send_counts.push_back(give_count[r]);
+    }
+    if (want_count[r] > 0)
+    {
+      L.recv_ranks.push_back(r);
+      L.recv_counts.push_back(want_count[r]);
+    }
+  }
+  L.send_idx.resize(give.size());
+  for (std::size_t i = 0; i < give.size(); ++i)
+    L.send_idx[i] = static_cast<std::int32_t>(give[i] - offset);
+  return L;
+}
+
 /// NCCL communicator + forward-scatter plan for one dolfinx::common::IndexMap.
 template <typename T>
 class HaloPlan
@@ -69,55 +134,13 @@ public:
     check(bd_comm_create(size > 1 ? id : nullptr, rank, size, &_comm));
     if (size == 1)
       return;
-
-    const std::int32_t n_owned = map.size_local();
-    const std::int64_t offset = map.local_range()[0];
-    std::span<const std::int64_t> ghosts = map.ghosts();
-    std::span<const int> owners = map.owners();
-    const std::size_t ng = ghosts.size();
-    // message order: ghosts grouped by owner rank (stable), position i of the messages is ghost order[i]
-    std::vector<std::int32_t> order(ng);
-    std::iota(order.begin(), order.end(), 0);
-    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return owners[a] < owners[b]; });
-    std::vector<int> want_count(size, 0);
-    for (std::size_t i = 0; i < ng; ++i)
-      ++want_count[owners[i]];
-    std::vector<int> want_displ(size + 1, 0);
-    std::partial_sum(want_count.begin(), want_count.end(), want_displ.begin() + 1);
-    std::vector<std::int64_t> want(ng);
-    for (std::size_t i = 0; i < ng; ++i)
-      want[i] = ghosts[order[i]];
-    // owners learn what to send
-    std::vector<int> give_count(size, 0);
-    MPI_Alltoall(want_count.data(), 1, MPI_INT, give_count.data(), 1, MPI_INT, comm);
-    std::vector<int> give_displ(size + 1, 0);
-    std::partial_sum(give_count.begin(), give_count.end(), give_displ.begin() + 1);
-    std::vector<std::int64_t> give(give_displ[size]);
-    MPI_Alltoallv(want.data(), want_count.data(), want_displ.data(), MPI_INT64_T, give.data(), give_count.data(),
-                  give_displ.data(), MPI_INT64_T, comm);
-
-    std::vector<std::int32_t> send_ranks, recv_ranks, send_idx(give.size());
-    std::vector<std::int64_t> send_counts, recv_counts;
-    for (int r = 0; r < size; ++r)
-    {
-      if (give_count[r] > 0)
-      {
-        send_ranks.push_back(r);
-        send_counts.push_back(give_count[r]);
-      }
-      if (want_count[r] > 0)
-      {
-        recv_ranks.push_back(r);
-        recv_counts.push_back(want_count[r]);
-      }
-    }
-    for (std::size_t i = 0; i < give.size(); ++i)
-      send_idx[i] = static_cast<std::int32_t>(give[i] - offset);
-    check(bd_halo_create(_comm, 8 * sizeof(T), n_owned, static_cast<std::int64_t>(ng),
-                         static_cast<int>(send_ranks.size()), send_ranks.data(), send_counts.data(), send_idx.data(),
-                         static_cast<int>(recv_ranks.size()), recv_ranks.data(), recv_counts.data(), &_halo));
-    if (!std::is_sorted(order.begin(), order.end()))
-      check(bd_halo_set_unpack(_halo, order.data()));
+    const HaloLists L = compute_halo_lists(map);
+    check(bd_halo_create(_comm, 8 * sizeof(T), map.size_local(), static_cast<std::int64_t>(map.num_ghosts()),
+                         static_cast<int>(L.send_ranks.size()), L.send_ranks.data(), L.send_counts.data(),
+                         L.send_idx.data(), static_cast<int>(L.recv_ranks.size()), L.recv_ranks.data(),
+                         L.recv_counts.data(), &_halo));
+    if (!L.ordered)
+      check(bd_halo_set_unpack(_halo, L.order.data()));
   }
   ~HaloPlan()
   {
