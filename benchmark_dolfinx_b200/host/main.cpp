@@ -213,6 +213,15 @@ int main(int argc, char* argv[])
       catch (const std::exception& e)
       {
         errors[rank] = e.what();
+        if (size > 1)
+        {
+          // The other ranks are (or will be) inside NCCL collectives that this rank will never join: leaving the
+          // barrier would let them hang.  Same outcome as an MPI rank of the reference dying in err_check
+          // (src/util.hpp:36-45: printf + exit(1)): the whole job ends.
+          std::fprintf(stderr, "rank %d: %s\n", rank, e.what());
+          std::fflush(stderr);
+          std::_Exit(1);
+        }
         sync.arrive_and_drop();
       }
     };
