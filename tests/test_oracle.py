@@ -201,3 +201,22 @@ def test_partitioned_oracle_equals_single_rank(nranks):
         # lcells touch no ghost dof; bcells = the rest incl. every ghost cell (src/mesh.cpp:154-188)
         assert (m.cell_dofmap[m.lcells] < m.ndofs_owned).all()
         assert len(m.lcells) + len(m.bcells) == m.ncells
+
+
+def test_oracle_jacobi_pcg_solves_the_assembled_system():
+    """The oracle's Jacobi-preconditioned CG (the checker of tests/test_gpu_jacobi.py) against a direct solve of the
+    oracle's assembled matrix, and never slower than plain CG in iterations."""
+    import scipy.sparse.linalg as spla
+    from oracle.laplacian import assemble_csr, assemble_rhs, cg_solve, pcg_solve_jacobi
+    for degree, qmode, perturb in ((2, 1, 0.2), (3, 0, 0.0)):
+        mesh = create_box_mesh(compute_mesh_size(2000, degree), degree, geom_perturb_fact=perturb)
+        t = Tables(degree, qmode)
+        A = assemble_csr(mesh, t, kappa=2.0)
+        b = assemble_rhs(mesh, t)
+        op = OracleLaplacian(mesh, t, kappa=2.0)
+        x = np.zeros_like(b)
+        its = pcg_solve_jacobi(op.apply, x, b, 1.0 / A.diagonal(), 500, rtol=1e-10)
+        x_direct = spla.spsolve(A.tocsc(), b)
+        assert np.linalg.norm(x - x_direct) / np.linalg.norm(x_direct) < 1e-8
+        its_plain = cg_solve(op.apply, np.zeros_like(b), b, 500, rtol=1e-10)
+        assert 0 < its <= its_plain
