@@ -61,13 +61,16 @@ __global__ void __launch_bounds__(256)
     const T K21 = -J[0][0] * J[2][1] + J[0][1] * J[2][0];
     const T K22 = J[0][0] * J[1][1] - J[0][1] * J[1][0];
     const T detJ = J[0][0] * K00 - J[0][1] * K10 + J[0][2] * K20;
+    // one division per point instead of the reference's six (`* w / detJ` per entry, src/geometry_gpu.hpp:113-130):
+    // fp64 divisions were 2/3 of this kernel's instructions; the entries differ from the reference's by <= 1.5 ulp
     const T w = __ldg(weights + q);
-    const T g0 = (K00 * K00 + K01 * K01 + K02 * K02) * w / detJ;
-    const T g1 = (K10 * K00 + K11 * K01 + K12 * K02) * w / detJ;
-    const T g2 = (K20 * K00 + K21 * K01 + K22 * K02) * w / detJ;
-    const T g3 = (K10 * K10 + K11 * K11 + K12 * K12) * w / detJ;
-    const T g4 = (K20 * K10 + K21 * K11 + K22 * K12) * w / detJ;
-    const T g5 = (K20 * K20 + K21 * K21 + K22 * K22) * w / detJ;
+    const T s = w / detJ;
+    const T g0 = (K00 * K00 + K01 * K01 + K02 * K02) * s;
+    const T g1 = (K10 * K00 + K11 * K01 + K12 * K02) * s;
+    const T g2 = (K20 * K00 + K21 * K01 + K22 * K02) * s;
+    const T g3 = (K10 * K10 + K11 * K11 + K12 * K12) * s;
+    const T g4 = (K20 * K10 + K21 * K11 + K22 * K12) * s;
+    const T g5 = (K20 * K20 + K21 * K21 + K22 * K22) * s;
     if constexpr (LAYOUT == 2)
     {
       const int q0 = q / (nq * nq), q1 = (q / nq) % nq, q2 = q % nq;
@@ -148,7 +151,7 @@ __global__ void __launch_bounds__(256)
           J[2][j] += x2 * d;
         }
       }
-      // same expressions and order as geometry_kernel (reference src/geometry_gpu.hpp:100-130)
+      // same expressions as geometry_kernel (reference src/geometry_gpu.hpp:100-130)
       const T K00 = J[1][1] * J[2][2] - J[1][2] * J[2][1];
       const T K01 = -J[0][1] * J[2][2] + J[0][2] * J[2][1];
       const T K02 = J[0][1] * J[1][2] - J[0][2] * J[1][1];
@@ -159,14 +162,14 @@ __global__ void __launch_bounds__(256)
       const T K21 = -J[0][0] * J[2][1] + J[0][1] * J[2][0];
       const T K22 = J[0][0] * J[1][1] - J[0][1] * J[1][0];
       const T detJ = J[0][0] * K00 - J[0][1] * K10 + J[0][2] * K20;
-      const T w = __ldg(weights + q);
+      const T sc = __ldg(weights + q) / detJ; // one division per point, see geometry_kernel
       T g[6];
-      g[0] = (K00 * K00 + K01 * K01 + K02 * K02) * w / detJ;
-      g[1] = (K10 * K00 + K11 * K01 + K12 * K02) * w / detJ;
-      g[2] = (K20 * K00 + K21 * K01 + K22 * K02) * w / detJ;
-      g[3] = (K10 * K10 + K11 * K11 + K12 * K12) * w / detJ;
-      g[4] = (K20 * K10 + K21 * K11 + K22 * K12) * w / detJ;
-      g[5] = (K20 * K20 + K21 * K21 + K22 * K22) * w / detJ;
+      g[0] = (K00 * K00 + K01 * K01 + K02 * K02) * sc;
+      g[1] = (K10 * K00 + K11 * K01 + K12 * K02) * sc;
+      g[2] = (K20 * K00 + K21 * K01 + K22 * K02) * sc;
+      g[3] = (K10 * K10 + K11 * K11 + K12 * K12) * sc;
+      g[4] = (K20 * K10 + K21 * K11 + K22 * K12) * sc;
+      g[5] = (K20 * K20 + K21 * K21 + K22 * K22) * sc;
       const int q0 = q / nq2, q1 = (q / nq) % nq, q2 = q % nq;
 #pragma unroll
       for (int comp = 0; comp < 6; ++comp)
