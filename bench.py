@@ -429,7 +429,7 @@ def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, samp
     # Its pipe fraction is computed from its OWN flop count; the rate in the reference algorithm's flops is kept as
     # `effective_gflops_reference_flop_count`.
     own_gflops = gflops
-    if "stiffness_affine_kernel" in common["kernel"]:
+    if "stiffness_affine" in common["kernel"]:     # both dof-space kernels
         own_gflops = 34 * (degree + 1) ** 4 * mesh.ncells / kernel_s / 1e9
         common["kernel_flops_per_dof"] = 34 * (degree + 1) ** 4 * mesh.ncells / mesh.ndofs_local
         common["effective_gflops_reference_flop_count"] = gflops

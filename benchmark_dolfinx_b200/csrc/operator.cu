@@ -229,19 +229,25 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
   const bool want_pre = (d->flags & BD_FLAG_GEOMETRY_PRECOMPUTED) != 0;
   if (want_otf && want_pre)
     return guard_fail(fail(BD_ERR_INVALID_ARGUMENT, "both geometry flags set"));
-  const bool otf_possible = !op->w1d.empty() && otf_supported(op->degree, op->nq);
-  if (want_otf && !otf_possible)
+  // a kernel for general cells exists for nq <= 8; on meshes of parallelepipeds the dof-space kernels also cover
+  // qmode 1 at every degree (nq = 9 included)
+  const bool tables_ok = !op->w1d.empty();
+  const bool otf_general = tables_ok && otf_supported(op->degree, op->nq);
+  const bool otf_affine = tables_ok && (otf_general || affine_dofspace_exists(op->degree, op->is_identity));
+  if (otf_affine && !want_pre)
+    TRY(d->scalar_bits == 64 ? count_nonaffine<double>(op) : count_nonaffine<float>(op));
+  if (want_otf && !(op->n_nonaffine == 0 ? otf_affine : otf_general))
     return guard_fail(fail(BD_ERR_UNSUPPORTED,
                            "on-the-fly geometry needs tensor-product quadrature weights, the trilinear coordinate "
-                           "element in tensor-product vertex order and nq <= 8 (nq = %d)", op->nq));
-  if (otf_possible && !want_pre)
-    TRY(d->scalar_bits == 64 ? count_nonaffine<double>(op) : count_nonaffine<float>(op));
-  // default: the shortcut kernel when every cell is a parallelepiped and it is the measured-faster choice for this
-  // (scalar type, nq) (otf_preferred); a stored G otherwise -- for general cells rebuilding G per point loses to
-  // streaming it (Q3 fp64 18.6 vs 20.1, Q6 26.8 vs 35.0, Q3 fp32 26.0 vs 34.8 GDoF/s)
+                           "element in tensor-product vertex order and, for cells that are not parallelepipeds, "
+                           "nq <= 8 (nq = %d, %lld such cells)", op->nq, (long long)op->n_nonaffine));
+  // default: the shortcut kernels when every cell is a parallelepiped and they are the measured-faster choice for
+  // this (scalar type, degree, nq) (otf_preferred); a stored G otherwise -- for general cells rebuilding G per point
+  // loses to streaming it (Q3 fp64 18.6 vs 20.1, Q6 26.8 vs 35.0, Q3 fp32 26.0 vs 34.8 GDoF/s)
   if (want_otf)
     op->geom_mode = op->n_nonaffine == 0 ? 1 : 2;
-  else if (!want_pre && otf_possible && op->n_nonaffine == 0 && otf_preferred(op->scalar_bits, op->degree, op->nq))
+  else if (!want_pre && otf_affine && op->n_nonaffine == 0
+           && otf_preferred(op->scalar_bits, op->degree, op->nq, op->is_identity))
     op->geom_mode = 1;
   else
     op->geom_mode = 0;
@@ -375,7 +381,9 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
                                                    : "bd::stiffness_slab_tma_kernel (register slabs, UBLKCP G ring)");
   if (op->geom_mode != 0)
   {
-    kernel = op->nq >= 7 ? "bd::stiffness_mma8_otf_kernel (fp64 DMMA m8n8k4 arithmetic, geometry on the fly)"
+    kernel = (op->geom_mode == 1 && affine_col_used(op->scalar_bits, op->degree, op->is_identity))
+                 ? "bd::stiffness_affine_col_kernel (dof-space 1-D operators M, S, C, column rounds; geometry on the fly)"
+             : op->nq >= 7 ? "bd::stiffness_mma8_otf_kernel (fp64 DMMA m8n8k4 arithmetic, geometry on the fly)"
              : (op->geom_mode == 1 && affine_kernel_used(op->scalar_bits, op->degree, op->is_identity))
                  ? "bd::stiffness_affine_kernel (dof-space 1-D operators M, S, C; geometry on the fly)"
                  : "bd::stiffness_slab_otf_kernel (register slabs, geometry on the fly)";

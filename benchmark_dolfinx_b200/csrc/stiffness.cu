@@ -75,6 +75,8 @@ int stiffness_dispatch(int scalar_bits, int degree, int nq, bool identity, const
     // geometry on the fly: slab kernel for nq <= 6, DMMA kernel for nq = 7, 8
     if (scalar_bits != 32 && scalar_bits != 64)
       return fail(BD_ERR_INVALID_ARGUMENT, "Invalid float size. Must be 32 or 64.");
+    if (a.geom_mode == 1 && affine_col_used(scalar_bits, degree, identity))
+      return launch_stiffness_affine_col_any(scalar_bits, degree, a);
     if (!otf_supported(degree, nq) || identity != (nq == degree + 1))
       return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry is not available for degree %d, nq %d", degree, nq);
     if (nq >= 7)

@@ -24,13 +24,44 @@
 
 namespace bd
 {
+// Rows are padded to a multiple of 16 bytes and C is also stored transposed, so that every use in the kernels reads a
+// contiguous, aligned row: the compiler then fetches two (fp64) or four (fp32) entries per constant-bank load.  M and S
+// are exactly symmetric (the host mirrors them), so their columns are their rows.
 template <typename T, int ND>
-struct AffineTables
+struct alignas(16) AffineTables
 {
-  T M[ND * ND]; // M[a][b] = sum_q w_q Phi[q][a] Phi[q][b]
-  T S[ND * ND]; // S[a][b] = sum_q w_q DPhi[q][a] DPhi[q][b]
-  T C[ND * ND]; // C[a][b] = sum_q w_q DPhi[q][a] Phi[q][b]
+  static constexpr int NDP = sizeof(T) == 8 ? (ND + 1) / 2 * 2 : (ND + 3) / 4 * 4;
+  T M[ND * NDP];  // M[a][b] = sum_q w_q Phi[q][a] Phi[q][b]
+  T S[ND * NDP];  // S[a][b] = sum_q w_q DPhi[q][a] DPhi[q][b]
+  T C[ND * NDP];  // C[a][b] = sum_q w_q DPhi[q][a] Phi[q][b]
+  T CT[ND * NDP]; // CT[a][b] = C[b][a]
 };
+
+// One padded table row (NDP entries, 16-byte aligned) with 16-byte constant-bank loads.
+template <typename T, int NDP>
+__device__ __forceinline__ void load_table_row(const T* __restrict__ table, int r, T (&out)[NDP])
+{
+  if constexpr (sizeof(T) == 8)
+  {
+    const double2* p = reinterpret_cast<const double2*>(table + r * NDP);
+#pragma unroll
+    for (int v = 0; v < NDP / 2; ++v)
+    {
+      const double2 x = p[v];
+      out[2 * v] = x.x, out[2 * v + 1] = x.y;
+    }
+  }
+  else
+  {
+    const float4* p = reinterpret_cast<const float4*>(table + r * NDP);
+#pragma unroll
+    for (int v = 0; v < NDP / 4; ++v)
+    {
+      const float4 x = p[v];
+      out[4 * v] = x.x, out[4 * v + 1] = x.y, out[4 * v + 2] = x.z, out[4 * v + 3] = x.w;
+    }
+  }
+}
 
 struct AffineStrides
 {
@@ -43,11 +74,11 @@ struct AffineStrides
 // bank-conflict free within each group of lanes the hardware serves together (16 lanes for 8-byte words, 32 for
 // 4-byte words).  With CH = CW the cell index is simply the fastest one; splitting it (CH = cells per 16-lane group)
 // needs less padding when the groups coincide with whole cells (nd = 4 in fp64: 20.5 KB per warp instead of 26).
-constexpr bool affine_strides_ok(int nd, bool is_double, int ch, int si, int sj)
+constexpr bool affine_strides_ok(int nd, bool is_double, int ch, int si, int sj, int kch)
 {
   const int cw = 32 / nd;
   const int nbanks = is_double ? 16 : 32, group = is_double ? 16 : 32;
-  const int hs = nd * nd * sj; // any multiple of the bank count in effect: only (c / ch) * hs mod nbanks matters
+  const int hs = kch * nd * sj;
   for (int pass = 0; pass < 2; ++pass)
     for (int g0 = 0; g0 < 32; g0 += group)
     {
@@ -65,7 +96,7 @@ constexpr bool affine_strides_ok(int nd, bool is_double, int ch, int si, int sj)
     }
   return true;
 }
-constexpr AffineStrides affine_strides(int nd, bool is_double)
+constexpr AffineStrides affine_strides(int nd, bool is_double, int kch)
 {
   const int cw = 32 / nd;
   AffineStrides best{cw, cw, nd * cw};
@@ -76,9 +107,9 @@ constexpr AffineStrides affine_strides(int nd, bool is_double)
       continue;
     for (int si = ch; si < ch + 33; ++si)
       for (int sj = nd * si; sj < nd * si + 33; ++sj)
-        if (affine_strides_ok(nd, is_double, ch, si, sj))
+        if (affine_strides_ok(nd, is_double, ch, si, sj, kch))
         {
-          const int size = (cw / ch) * nd * nd * sj;
+          const int size = (cw / ch) * kch * nd * sj;
           if (size < best_size)
           {
             best_size = size;
@@ -90,14 +121,17 @@ constexpr AffineStrides affine_strides(int nd, bool is_double)
   return best;
 }
 
-template <typename T, int P, int WARPS_, int KCH_>
+// COMPACT: no padding at all (cell index fastest, then i, then j): the phase-B reads then have 2-way bank conflicts for
+// some nd, which costs little where the exchange is a small part of the work (column-round kernel) and buys occupancy.
+template <typename T, int P, int WARPS_, int KCH_, bool COMPACT = false>
 struct AffineConfig
 {
   static constexpr int ND = P + 1;
   static constexpr int KCH = KCH_; // output columns k per exchange round (divides ND)
   static_assert(ND % KCH_ == 0, "KCH must divide nd");
   static constexpr int CW = 32 / ND;
-  static constexpr AffineStrides ST = affine_strides(ND, sizeof(T) == 8);
+  static constexpr AffineStrides ST = COMPACT ? AffineStrides{32 / (P + 1), 32 / (P + 1), (P + 1) * (32 / (P + 1))}
+                                              : affine_strides(ND, sizeof(T) == 8, KCH_);
   static constexpr int CH = ST.ch, SI = ST.si, SJ = ST.sj, SK = ND * SJ, HS = KCH * SK, PL = (CW / CH) * HS;
   static constexpr int WARP_BYTES = (4 * PL * int(sizeof(T)) + 15) / 16 * 16;
   static constexpr int WARPS = WARPS_;
@@ -114,7 +148,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
 {
   using AC = AffineConfig<T, P, WARPS_, KCH>;
   constexpr int ND = AC::ND, CW = AC::CW, SI = AC::SI, SJ = AC::SJ, SK = AC::SK, PL = AC::PL;
-  constexpr int ND2 = ND * ND, ND3 = ND2 * ND;
+  constexpr int ND2 = ND * ND, ND3 = ND2 * ND, NDP = AffineTables<T, ND>::NDP;
   constexpr bool DEEP = sizeof(T) == 8;
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
@@ -278,29 +312,41 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
       {
         const int k1 = r * KCH + kk;
         T mz[ND], sz[ND], cz[ND], ctz[ND]; // (M_z u, S_z u, C_z u, C^T_z u)[j][k1]
-#pragma unroll
-        for (int j = 0; j < ND; ++j)
         {
-          T a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+          T Mr[NDP], Sr[NDP], Cr[NDP], Ctr[NDP];
+          load_table_row<T, NDP>(tab.M, k1, Mr);
+          load_table_row<T, NDP>(tab.S, k1, Sr);
+          load_table_row<T, NDP>(tab.C, k1, Cr);
+          load_table_row<T, NDP>(tab.CT, k1, Ctr);
 #pragma unroll
-          for (int k = 0; k < ND; ++k)
+          for (int j = 0; j < ND; ++j)
           {
-            const T v = ul[j * ND + k];
-            a0 = fma(tab.M[k1 * ND + k], v, a0);
-            a1 = fma(tab.S[k1 * ND + k], v, a1);
-            a2 = fma(tab.C[k1 * ND + k], v, a2);
-            a3 = fma(tab.C[k * ND + k1], v, a3);
+            T a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+#pragma unroll
+            for (int k = 0; k < ND; ++k)
+            {
+              const T v = ul[j * ND + k];
+              a0 = fma(Mr[k], v, a0);
+              a1 = fma(Sr[k], v, a1);
+              a2 = fma(Cr[k], v, a2);  // C_z
+              a3 = fma(Ctr[k], v, a3); // C^T_z
+            }
+            mz[j] = a0, sz[j] = a1, cz[j] = a2, ctz[j] = a3;
           }
-          mz[j] = a0, sz[j] = a1, cz[j] = a2, ctz[j] = a3;
         }
 #pragma unroll 1
         for (int j1 = 0; j1 < ND; ++j1)
         {
           T p1 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0, s6 = 0, s7 = 0;
+          T Mr[NDP], Sr[NDP], Cr[NDP], Ctr[NDP];
+          load_table_row<T, NDP>(tab.M, j1, Mr);
+          load_table_row<T, NDP>(tab.S, j1, Sr);
+          load_table_row<T, NDP>(tab.C, j1, Cr);
+          load_table_row<T, NDP>(tab.CT, j1, Ctr);
 #pragma unroll
           for (int j = 0; j < ND; ++j)
           {
-            const T Mj = tab.M[j1 * ND + j], Sj = tab.S[j1 * ND + j], Cj = tab.C[j1 * ND + j], Ctj = tab.C[j * ND + j1];
+            const T Mj = Mr[j], Sj = Sr[j], Cj = Cr[j], Ctj = Ctr[j];
             p1 = fma(Mj, mz[j], p1);                   // M_y M_z
             s1 = fma(Sj, mz[j], s1);                   // S_y M_z
             s2 = fma(Mj, sz[j], s2);                   // M_y S_z
@@ -352,10 +398,16 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
             const T* src = buf + kk * SK + m * SJ + i * SI;
             q1[kk] = src[0], q2[kk] = src[PL], q3[kk] = src[2 * PL], q4[kk] = src[3 * PL];
           }
+          // column i of S, M, C and row i of C: all read as rows (S, M symmetric; CT = C transposed)
+          T Sr[NDP], Mr[NDP], Ctr[NDP], Cr[NDP];
+          load_table_row<T, NDP>(tab.S, i, Sr);
+          load_table_row<T, NDP>(tab.M, i, Mr);
+          load_table_row<T, NDP>(tab.CT, i, Ctr);
+          load_table_row<T, NDP>(tab.C, i, Cr);
 #pragma unroll
           for (int i1 = 0; i1 < ND; ++i1)
           {
-            const T Si = tab.S[i1 * ND + i], Mi = tab.M[i1 * ND + i], Ci = tab.C[i1 * ND + i], Cti = tab.C[i * ND + i1];
+            const T Si = Sr[i1], Mi = Mr[i1], Ci = Ctr[i1], Cti = Cr[i1];
 #pragma unroll
             for (int kk = 0; kk < KCH; ++kk)
             {

@@ -8,6 +8,7 @@
 #include "stiffness_pencil_bulk.cuh"
 #include "stiffness_slab_otf.cuh"
 #include "stiffness_affine.cuh"
+#include "stiffness_affine_col.cuh"
 
 namespace bd
 {
@@ -288,6 +289,35 @@ constexpr bool affine_kernel_used(int scalar_bits, int degree, bool identity)
   return !identity && (degree <= 3 || (degree == 4 && scalar_bits == 32));
 }
 
+// Host-side 1-D operators M, S, C of the dof-space kernels, from the operator's own tables (in double).
+template <typename T, int ND, int NQ, bool IDENTITY>
+void fill_affine_tables(AffineTables<T, ND>& tab, const StiffnessArgs& a)
+{
+  SlabTables<T, ND, NQ> st;
+  fill_slab_tables<T, ND, NQ, IDENTITY>(st, a.phi0_host, a.dphi1_host);
+  constexpr int NDP = AffineTables<T, ND>::NDP;
+  for (int i = 0; i < ND * NDP; ++i)
+    tab.M[i] = tab.S[i] = tab.C[i] = tab.CT[i] = T(0);
+  for (int r = 0; r < ND; ++r)
+    for (int c = 0; c < ND; ++c)
+    {
+      // M and S from the (r <= c) triangle and mirrored: exactly symmetric, the kernels read their columns as rows
+      const int a0 = r < c ? r : c, b0 = r < c ? c : r;
+      double m = 0, sv = 0, cv = 0;
+      for (int q = 0; q < NQ; ++q)
+      {
+        const double w = a.w1d[q];
+        m += w * st.phi[q * ND + a0] * st.phi[q * ND + b0];
+        sv += w * st.dphi[q * ND + a0] * st.dphi[q * ND + b0];
+        cv += w * st.dphi[q * ND + r] * st.phi[q * ND + c];
+      }
+      tab.M[r * NDP + c] = static_cast<T>(m);
+      tab.S[r * NDP + c] = static_cast<T>(sv);
+      tab.C[r * NDP + c] = static_cast<T>(cv);
+      tab.CT[c * NDP + r] = static_cast<T>(cv);
+    }
+}
+
 // Dof-space kernel for meshes of parallelepipeds (stiffness_affine.cuh), degree <= 3.
 template <typename T, int P, int NQ, bool IDENTITY, int MINB, int KCH>
 int launch_stiffness_affine(const StiffnessArgs& a)
@@ -313,31 +343,49 @@ int launch_stiffness_affine(const StiffnessArgs& a)
     BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, AC::THREADS, AC::CTA_SMEM));
     blocks_per_sm[dev] = nb > 0 ? nb : 1;
   }
-  // 1-D matrices in double from the operator's own tables: Phi, DPhi = dphi1 * phi0 (or dphi1 when Phi = I)
-  SlabTables<T, ND, NQ> st;
-  fill_slab_tables<T, ND, NQ, IDENTITY>(st, a.phi0_host, a.dphi1_host);
   AffineTables<T, ND> tab;
-  for (int r = 0; r < ND; ++r)
-    for (int c = 0; c < ND; ++c)
-    {
-      double m = 0, sv = 0, cv = 0;
-      for (int q = 0; q < NQ; ++q)
-      {
-        const double w = a.w1d[q];
-        const double pr = st.phi[q * ND + r], pc = st.phi[q * ND + c];
-        const double dr = st.dphi[q * ND + r], dc = st.dphi[q * ND + c];
-        m += w * pr * pc;
-        sv += w * dr * dc;
-        cv += w * dr * pc;
-      }
-      tab.M[r * ND + c] = static_cast<T>(m);
-      tab.S[r * ND + c] = static_cast<T>(sv);
-      tab.C[r * ND + c] = static_cast<T>(cv);
-    }
+  fill_affine_tables<T, ND, NQ, IDENTITY>(tab, a);
   const std::int64_t nbatches = (a.ncells + AC::CW - 1) / AC::CW;
   const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
   const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
   kernel<<<grid, AC::THREADS, AC::CTA_SMEM, a.stream>>>(
+      static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.xgeom), a.gdofmap,
+      static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+// Dof-space kernel with the plane in shared memory and column rounds (stiffness_affine_col.cuh), degree 4..7.
+template <typename T, int P, int NQ, bool IDENTITY, int MINB, bool COMPACT>
+int launch_stiffness_affine_col(const StiffnessArgs& a)
+{
+  constexpr int ND = P + 1;
+  using CC = AffineColConfig<T, P, 1, COMPACT>;
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d)
+    return fail(BD_ERR_INVALID_ARGUMENT, "the affine-cell kernel needs the masked dofmap, vertices and 1-D rule");
+  auto kernel = stiffness_affine_col_kernel<T, P, 1, MINB, COMPACT>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CC::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, CC::THREADS, CC::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  AffineTables<T, ND> tab;
+  fill_affine_tables<T, ND, NQ, IDENTITY>(tab, a);
+  const std::int64_t nbatches = (a.ncells + CC::CW - 1) / CC::CW;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
+  kernel<<<grid, CC::THREADS, CC::CTA_SMEM, a.stream>>>(
       static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.xgeom), a.gdofmap,
       static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
   BD_CUDA_CHECK(cudaGetLastError());
@@ -515,8 +563,28 @@ int launch_stiffness_otf_f64_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_otf_f64_q1(int degree, const StiffnessArgs& a);
 int launch_stiffness_otf_f32_q0(int degree, const StiffnessArgs& a);
 int launch_stiffness_otf_f32_q1(int degree, const StiffnessArgs& a);
+// in stiffness_affine_col.cu: dof-space kernel for parallelepiped cells, degree 4..7, qmode 1
+int launch_stiffness_affine_col_any(int scalar_bits, int degree, const StiffnessArgs& a);
 // in stiffness_mma8.cu: on-the-fly geometry for nq = 7, 8
 int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const StiffnessArgs& a);
+// The column-round dof-space kernel (stiffness_affine_col.cuh) exists for qmode 1 at degree 4..7 ...
+constexpr bool affine_dofspace_exists(int degree, bool identity) { return !identity && degree >= 1 && degree <= 7; }
+// ... and is used where it measured faster than the alternatives on one B200 (profiles/r2_affine_col_ab.txt, GDoF/s):
+//   fp64: degree 4 46.6 (quadrature-space on the fly 32.1), degree 5 47.5 (stored G, DMMA 24.6), degree 7 38.8 (stored G,
+//         pencils 21.1); NOT degree 6, where the DMMA on-the-fly kernel is a hair ahead (37.9 vs 37.3);
+//   fp32: degree 5 67.6 (stored G 32.5), degree 6 61.4 (50.3), degree 7 60.6 (41.3); NOT degree 4, where the
+//         register-plane kernel of stiffness_affine.cuh does 70.2.
+constexpr bool affine_col_used(int scalar_bits, int degree, bool identity)
+{
+  if (identity)
+    return false;
+  return scalar_bits == 64 ? (degree == 4 || degree == 5 || degree == 7) : (degree == 5 || degree == 6 || degree == 7);
+}
+// unpadded exchange buffer (2-way bank conflicts on its reads for some nd, more warps per SM): where it measured faster
+constexpr bool affine_col_compact(int scalar_bits, int degree)
+{
+  return scalar_bits == 64 ? degree == 4 : (degree == 5 || degree == 6);
+}
 // on-the-fly geometry exists for this (degree, nq)?
 inline bool otf_supported(int degree, int nq) { return nq >= 2 && nq <= 8 && (nq == degree + 1 || nq == degree + 2); }
 // ... and is the measured-faster choice on a mesh of parallelepipeds (profiles/r2_onthefly_*_ab.txt, one B200)?
@@ -525,8 +593,10 @@ inline bool otf_supported(int degree, int nq) { return nq >= 2 && nq <= 8 && (nq
 //           the G stream), 78.2 vs 51.4 at Q7 qmode 0 -> on the fly (and 56 GB less memory, no G precompute);
 //   nq = 7, fp64: on the fly wins with Phi = I (Q6 qmode 0: 59.5 vs 52.9), stored G wins at qmode 1 (Q5: 24.6 vs 23.4);
 //   fp32 with nq >= 7: the pencil kernels with a stored G win (50.3 vs 34.8 GDoF/s at Q6) -> stored G.
-inline bool otf_preferred(int scalar_bits, int degree, int nq)
+inline bool otf_preferred(int scalar_bits, int degree, int nq, bool identity)
 {
+  if (affine_col_used(scalar_bits, degree, identity))
+    return true;
   return otf_supported(degree, nq)
          && (nq <= 6 || (scalar_bits == 64 && (nq == 8 || (nq == 7 && nq == degree + 1))));
 }

@@ -69,7 +69,7 @@ def grid_cap():
     bd.debug_set_max_grid(0)
 
 
-_PQ = [(p, q) for p in range(1, 8) for q in (0, 1) if p + 1 + q <= 8]
+_PQ = [(p, q) for p in range(1, 8) for q in (0, 1)]
 
 
 @pytest.mark.parametrize("kind", ["box", "sheared", "perturbed", "mixed"])
@@ -79,6 +79,11 @@ def test_onthefly_matches_oracle(degree, qmode, dtype, kind, grid_cap):
     import torch
     import benchmark_dolfinx_b200 as bd
     m, u, y_ref, G_ref = _cached(degree, qmode, kind)
+    if degree + 1 + qmode == 9 and kind in ("perturbed", "mixed"):
+        # nq = 9 has a kernel for parallelepiped cells only (the dof-space one): general cells must be refused
+        with pytest.raises(bd.BenchDolfinxError):
+            bd.MatFreeLaplacianGPU(m, degree, qmode, 2.0, dtype=dtype, geometry="onthefly")
+        return
     op = bd.MatFreeLaplacianGPU(m, degree, qmode, 2.0, dtype=dtype, geometry="onthefly")
     mode, nonaffine = op.geometry_mode()
     if kind in ("box", "sheared") and dtype == np.float64:
@@ -113,11 +118,14 @@ def test_default_choice_and_forced_modes():
         pre.apply(ud, y2)
         torch.cuda.synchronize()
         assert _rel(y1.cpu().numpy(), y_ref) < 1e-12 and _rel(y2.cpu().numpy(), y_ref) < 1e-12
-    # nq = 9 has no on-the-fly kernel: forcing it is an error, the default falls back to a stored G
+    # every degree has a dof-space kernel for parallelepipeds at qmode 1 (nq = 9 included) ...
     m7 = create_box_mesh(compute_mesh_size(3000, 7), 7)
-    with pytest.raises(bd.BenchDolfinxError):
-        bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0, geometry="onthefly")
-    assert bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0).geometry_mode()[0] == "precomputed"
+    op7 = bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0)
+    assert op7.geometry_mode()[0] == "onthefly-affine" and "affine_col" in op7.describe()
+    # ... and the DMMA on-the-fly kernel stays the choice at degree 6 in fp64, the stored G at degree 6 qmode 0 in fp32
+    m6 = create_box_mesh(compute_mesh_size(3000, 6), 6)
+    assert "mma8_otf" in bd.MatFreeLaplacianGPU(m6, 6, 1, 2.0).describe()
+    assert "affine_col" in bd.MatFreeLaplacianGPU(m6, 6, 1, 2.0, dtype=np.float32).describe()
 
 
 def test_onthefly_cg_and_csr_check():
