@@ -202,13 +202,29 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
       }
       __syncwarp();
 
-      // x contraction for (., j = m, k1) and scatter
+      // x contraction for (., j = m, k1) and scatter.  Four accumulators per output (one per operator) instead of one
+      // nested chain: 4 nd independent multiply-adds per input plane i instead of nd chains of depth 4.
       if (lane_ok)
       {
-        T out[ND];
+        // scatter indices first: dof (i1, j = m, k1) at srow[i1 * ND2]; in flight during the contraction
+        std::int32_t sd[ND];
+        if (row)
+        {
+          const std::int32_t* srow = row + m * ND + k1;
+#pragma unroll
+          for (int i1 = 0; i1 < ND; ++i1)
+            sd[i1] = srow[i1 * ND2];
+        }
+        else
+        {
+#pragma unroll
+          for (int i1 = 0; i1 < ND; ++i1)
+            sd[i1] = kBcBit;
+        }
+        T oS[ND], oM[ND], oC[ND], oT[ND];
 #pragma unroll
         for (int i1 = 0; i1 < ND; ++i1)
-          out[i1] = 0;
+          oS[i1] = oM[i1] = oC[i1] = oT[i1] = 0;
 #pragma unroll 1
         for (int i = 0; i < ND; ++i)
         {
@@ -222,19 +238,17 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
           load_table_row<T, NDP>(tab.C, i, Cr);
 #pragma unroll
           for (int i1 = 0; i1 < ND; ++i1)
-            out[i1] = fma(Sr[i1], q1, fma(Mr[i1], q2, fma(Ctr[i1], q3, fma(Cr[i1], q4, out[i1]))));
-        }
-        if (row)
-        {
-          const std::int32_t* srow = row + m * ND + k1; // dof (i1, j = m, k1) at srow[i1 * ND2]
-#pragma unroll
-          for (int i1 = 0; i1 < ND; ++i1)
           {
-            const std::int32_t d = srow[i1 * ND2];
-            if (d >= 0)
-              atomicAdd(y + d, out[i1]); // result unused -> RED.E.ADD (reference :424-425)
+            oS[i1] = fma(Sr[i1], q1, oS[i1]);
+            oM[i1] = fma(Mr[i1], q2, oM[i1]);
+            oC[i1] = fma(Ctr[i1], q3, oC[i1]);
+            oT[i1] = fma(Cr[i1], q4, oT[i1]);
           }
         }
+#pragma unroll
+        for (int i1 = 0; i1 < ND; ++i1)
+          if (sd[i1] >= 0)
+            atomicAdd(y + sd[i1], (oS[i1] + oM[i1]) + (oC[i1] + oT[i1])); // result unused -> RED.E.ADD (reference :424-425)
       }
       __syncwarp(); // the exchange buffer is rewritten by the next round
     }
