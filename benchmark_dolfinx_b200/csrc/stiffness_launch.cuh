@@ -587,18 +587,17 @@ constexpr bool affine_col_compact(int scalar_bits, int degree)
 }
 // on-the-fly geometry exists for this (degree, nq)?
 inline bool otf_supported(int degree, int nq) { return nq >= 2 && nq <= 8 && (nq == degree + 1 || nq == degree + 2); }
-// ... and is the measured-faster choice on a mesh of parallelepipeds (profiles/r2_onthefly_*_ab.txt, one B200)?
-//   nq <= 6 (slab kernel): yes for both scalar types (fp64 1.45-1.7x, fp32 1.3x over streaming G);
-//   nq = 8, fp64 (DMMA kernel): 37.8 vs 34.4 GDoF/s at Q6 qmode 1 (that kernel is bound by its arithmetic, not by
-//           the G stream), 78.2 vs 51.4 at Q7 qmode 0 -> on the fly (and 56 GB less memory, no G precompute);
-//   nq = 7, fp64: on the fly wins with Phi = I (Q6 qmode 0: 59.5 vs 52.9), stored G wins at qmode 1 (Q5: 24.6 vs 23.4);
-//   fp32 with nq >= 7: the pencil kernels with a stored G win (50.3 vs 34.8 GDoF/s at Q6) -> stored G.
+// ... and is the measured-faster choice on a mesh of parallelepipeds (profiles/r2_onthefly_*_ab.txt, r2_affine*_ab.txt,
+// one B200) -- which, with the dof-space kernels, is now every (scalar type, degree, qmode):
+//   qmode 1: the dof-space kernels (affine_kernel_used / affine_col_used), Q6 fp64 excepted (DMMA on the fly, 37.9 vs 37.3);
+//   qmode 0, nq <= 6 (slab kernel): fp64 1.45-1.7x, fp32 1.35-1.5x over streaming G;
+//   qmode 0, nq = 7 (DMMA kernel): fp64 59.5 vs 52.9, fp32 60.1 vs 22.3 GDoF/s;
+//   qmode 0, nq = 8 (DMMA kernel): fp64 78.2 vs 51.4, fp32 85.7 vs 85.6 (a tie: on the fly for the memory).
 inline bool otf_preferred(int scalar_bits, int degree, int nq, bool identity)
 {
-  if (affine_col_used(scalar_bits, degree, identity))
+  if (affine_kernel_used(scalar_bits, degree, identity) || affine_col_used(scalar_bits, degree, identity))
     return true;
-  return otf_supported(degree, nq)
-         && (nq <= 6 || (scalar_bits == 64 && (nq == 8 || (nq == 7 && nq == degree + 1))));
+  return otf_supported(degree, nq) && (nq <= 6 || nq == 8 || (nq == 7 && identity));
 }
 
 // in geometry.cu
