@@ -63,6 +63,9 @@ __device__ __forceinline__ void load_table_row(const T* __restrict__ table, int 
   }
 }
 
+// Unroll factor of the row loops of stiffness_affine_kernel (measured, profiles/r2_affine_ab.txt): two iterations at a time
+// in fp64 (Q3 48.4 -> 50.7 GDoF/s; four spill: 33.6), everything in fp32 and at nd = 2 (Q4 fp32 70.2 -> 76.2, Q1 16.2 -> 18.3).
+constexpr int affine_unroll(bool is_double, int nd) { return (!is_double || nd == 2) ? 4 : 2; }
 struct AffineStrides
 {
   int ch, si, sj; // cells per group of the cell index, strides of i and j
@@ -150,6 +153,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   constexpr int ND = AC::ND, CW = AC::CW, SI = AC::SI, SJ = AC::SJ, SK = AC::SK, PL = AC::PL;
   constexpr int ND2 = ND * ND, ND3 = ND2 * ND, NDP = AffineTables<T, ND>::NDP;
   constexpr bool DEEP = sizeof(T) == 8;
+  constexpr int kAffineUnroll = affine_unroll(sizeof(T) == 8, ND);
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;
@@ -334,7 +338,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
             mz[j] = a0, sz[j] = a1, cz[j] = a2, ctz[j] = a3;
           }
         }
-#pragma unroll 1
+#pragma unroll kAffineUnroll
         for (int j1 = 0; j1 < ND; ++j1)
         {
           T p1 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0, s6 = 0, s7 = 0;
@@ -388,7 +392,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
       // Phase B: x contraction for the column j = m and the round's k columns (loop over the input plane i rolled)
       if (lane_ok)
       {
-#pragma unroll 1
+#pragma unroll kAffineUnroll
         for (int i = 0; i < ND; ++i)
         {
           T q1[KCH], q2[KCH], q3[KCH], q4[KCH];
