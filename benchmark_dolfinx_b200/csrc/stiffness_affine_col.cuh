@@ -50,8 +50,9 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   using AC = typename CC::X;
   constexpr int ND = CC::ND, CW = CC::CW, ND2 = CC::ND2, ND3 = ND2 * ND, NDP = AffineTables<T, ND>::NDP;
   constexpr int SI = AC::SI, SJ = AC::SJ, PL = AC::PL;
-  // row loops two iterations at a time (measured +1-4 % over one; profiles/r2_affine_col_ab.txt)
-  constexpr int kColUnroll = 2;
+  // row loops four iterations at a time (measured: fp64 Q6 35.4 / 38.6 / 40.3 / 40.6 GDoF/s with 1 / 2 / 4 / all, but all
+  // spills at nd = 8 and loses at nd = 5, 6; profiles/r2_affine_col_ab.txt)
+  constexpr int kColUnroll = 4;
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;

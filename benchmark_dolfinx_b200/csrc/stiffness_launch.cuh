@@ -570,26 +570,27 @@ int launch_stiffness_mma8_otf(int scalar_bits, int degree, bool identity, const 
 // The column-round dof-space kernel (stiffness_affine_col.cuh) exists for qmode 1 at degree 4..7 ...
 constexpr bool affine_dofspace_exists(int degree, bool identity) { return !identity && degree >= 1 && degree <= 7; }
 // ... and is used where it measured faster than the alternatives on one B200 (profiles/r2_affine_col_ab.txt, GDoF/s):
-//   fp64: degree 4 46.6 (quadrature-space on the fly 32.1), degree 5 47.5 (stored G, DMMA 24.6), degree 7 38.8 (stored G,
-//         pencils 21.1); NOT degree 6, where the DMMA on-the-fly kernel is a hair ahead (37.9 vs 37.3);
-//   fp32: degree 5 67.6 (stored G 32.5), degree 6 61.4 (50.3), degree 7 60.6 (41.3); NOT degree 4, where the
-//         register-plane kernel of stiffness_affine.cuh does 70.2.
+//   fp64: degree 4 46.7 (quadrature-space on the fly 32.1), degree 5 49.3 (stored G, DMMA 24.6), degree 6 40.3 (DMMA on
+//         the fly 37.9, stored G 34.7), degree 7 40.7 (stored G, pencils 21.1);
+//   fp32: degree 5 74.3 (stored G 32.5), degree 6 68.8 (50.3), degree 7 62.3 (41.3); NOT degree 4, where the
+//         register-plane kernel of stiffness_affine.cuh does 76.2.
 constexpr bool affine_col_used(int scalar_bits, int degree, bool identity)
 {
   if (identity)
     return false;
-  return scalar_bits == 64 ? (degree == 4 || degree == 5 || degree == 7) : (degree == 5 || degree == 6 || degree == 7);
+  return scalar_bits == 64 ? (degree >= 4 && degree <= 7) : (degree == 5 || degree == 6 || degree == 7);
 }
 // unpadded exchange buffer (2-way bank conflicts on its reads for some nd, more warps per SM): where it measured faster
+// or equal
 constexpr bool affine_col_compact(int scalar_bits, int degree)
 {
-  return scalar_bits == 64 ? degree == 4 : (degree == 5 || degree == 6);
+  return scalar_bits == 64 ? (degree == 4 || degree == 6) : (degree == 5 || degree == 6);
 }
 // on-the-fly geometry exists for this (degree, nq)?
 inline bool otf_supported(int degree, int nq) { return nq >= 2 && nq <= 8 && (nq == degree + 1 || nq == degree + 2); }
 // ... and is the measured-faster choice on a mesh of parallelepipeds (profiles/r2_onthefly_*_ab.txt, r2_affine*_ab.txt,
 // one B200) -- which, with the dof-space kernels, is now every (scalar type, degree, qmode):
-//   qmode 1: the dof-space kernels (affine_kernel_used / affine_col_used), Q6 fp64 excepted (DMMA on the fly, 37.9 vs 37.3);
+//   qmode 1: the dof-space kernels (affine_kernel_used / affine_col_used);
 //   qmode 0, nq <= 6 (slab kernel): fp64 1.45-1.7x, fp32 1.35-1.5x over streaming G;
 //   qmode 0, nq = 7 (DMMA kernel): fp64 59.5 vs 52.9, fp32 60.1 vs 22.3 GDoF/s;
 //   qmode 0, nq = 8 (DMMA kernel): fp64 78.2 vs 51.4, fp32 85.7 vs 85.6 (a tie: on the fly for the memory).

@@ -122,10 +122,11 @@ def test_default_choice_and_forced_modes():
     m7 = create_box_mesh(compute_mesh_size(3000, 7), 7)
     op7 = bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0)
     assert op7.geometry_mode()[0] == "onthefly-affine" and "affine_col" in op7.describe()
-    # ... and the DMMA on-the-fly kernel stays the choice at degree 6 in fp64, the stored G at degree 6 qmode 0 in fp32
+    # ... while qmode 0 keeps the quadrature-space kernels (Phi = I makes them the cheaper ones): DMMA at nq = 7
     m6 = create_box_mesh(compute_mesh_size(3000, 6), 6)
-    assert "mma8_otf" in bd.MatFreeLaplacianGPU(m6, 6, 1, 2.0).describe()
+    assert "affine_col" in bd.MatFreeLaplacianGPU(m6, 6, 1, 2.0).describe()
     assert "affine_col" in bd.MatFreeLaplacianGPU(m6, 6, 1, 2.0, dtype=np.float32).describe()
+    assert "mma8_otf" in bd.MatFreeLaplacianGPU(m6, 6, 0, 2.0).describe()
 
 
 def test_onthefly_cg_and_csr_check():
