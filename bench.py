@@ -426,13 +426,15 @@ def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, samp
         "fp_gflops_algorithmic": gflops,
     }
     # The dof-space kernel for parallelepiped cells runs a different (cheaper) algorithm than the quadrature loop
-    # SURVEY.md section 8(d) counts: 17 applications of an nd x nd matrix per dof plane = 34 nd^4 flops per cell.
+    # SURVEY.md section 8(d) counts: 17 applications of an nd x nd matrix per dof plane = 34 nd^4 flops per cell
+    # (7 applications = 14 nd^4 when every cell is a brick and G_cell is diagonal).
     # Its pipe fraction is computed from its OWN flop count; the rate in the reference algorithm's flops is kept as
     # `effective_gflops_reference_flop_count`.
     own_gflops = gflops
     if "stiffness_affine" in common["kernel"]:     # both dof-space kernels
-        own_gflops = 34 * (degree + 1) ** 4 * mesh.ncells / kernel_s / 1e9
-        common["kernel_flops_per_dof"] = 34 * (degree + 1) ** 4 * mesh.ncells / mesh.ndofs_local
+        per_cell = (14 if mode == "onthefly-brick" else 34) * (degree + 1) ** 4
+        own_gflops = per_cell * mesh.ncells / kernel_s / 1e9
+        common["kernel_flops_per_dof"] = per_cell * mesh.ncells / mesh.ndofs_local
         common["effective_gflops_reference_flop_count"] = gflops
     fp = None
     if FP64_PEAKS is not None:
@@ -492,7 +494,7 @@ def parity_leg(ctx, bd, geometry):
         n = bd.compute_mesh_size(ndofs, 3)
         mesh = bd.BoxMesh(n, 3, ctx.rank, ctx.world)
         halo = bd.Halo(ctx.comm, mesh) if ctx.world > 1 else None
-        for geo in sorted({"precomputed", geometry}):
+        for geo in sorted({"precomputed", geometry, "auto-full"}):
             op = bd.MatFreeLaplacianGPU(mesh, 3, qmode, 2.0, halo=halo, geometry=geo)
             u = mesh.assemble_rhs(qmode)
             y = torch.zeros_like(u)
@@ -597,11 +599,12 @@ def main():
                     help="fixed global size (strong scaling, reference --ndofs_global); overrides --ndofs")
     ap.add_argument("--float", type=int, default=64, choices=[32, 64])
     ap.add_argument("--qmode", type=int, default=1, choices=[0, 1])
-    ap.add_argument("--geometry", default="auto", choices=["auto", "precomputed", "onthefly"],
+    ap.add_argument("--geometry", default="auto", choices=["auto", "precomputed", "onthefly", "auto-full", "onthefly-full"],
                     help="geometry variant of the headline legs: G precomputed and streamed (what the reference does), "
                          "rebuilt on the fly in the stiffness kernel, or auto = the operator's own choice (on the fly "
-                         "when every cell is a parallelepiped).  The other variant is measured too and reported "
-                         "under `variants`")
+                         "when every cell is a parallelepiped; on meshes of bricks -- the benchmark's own box -- the dof-space "
+                         "kernels then also use that G_cell is diagonal; *-full = without that shortcut).  The other "
+                         "variants are measured too and reported under `variants`")
     ap.add_argument("--geom_perturb_fact", type=float, default=0.0,
                     help="random perturbation of the mesh vertices as a fraction of the cell size (reference option "
                          "of the same name, src/main.cpp:163); 0 = the benchmark's unperturbed box")
@@ -676,21 +679,24 @@ def main():
     variants = {head_mode: {"value": head["value"], "ms_per_step": head["ms_per_step"], "roofline": head["roofline"],
                             "cg": cg and cg["value"], "y_norm": ynorm, "headline": True}}
     if not args.no_variants:
-        other = "precomputed" if head_mode != "precomputed" else "onthefly"
-        try:
-            op2 = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, halo=halo, geometry=other)
-            leg = action_leg(ctx, bd, mesh, op2, u, y, args.steps, args.warmup, degree, qmode, args.float)
-            yn2 = bd.norm(y, mesh.ndofs_owned, comm)
-            cg2 = None if args.no_cg else cg_leg(ctx, bd, mesh, op2, u, args.steps, args.warmup,
-                                                 leg["roofline"]["algorithmic_bytes_per_apply"], tsize)
-            variants[leg["geometry"]] = {"value": leg["value"], "ms_per_step": leg["ms_per_step"],
-                                         "roofline": leg["roofline"], "cg": cg2 and cg2["value"], "y_norm": yn2,
-                                         "halo": leg["halo"],
-                                         "rel_diff_y_norm_vs_headline": abs(yn2 - ynorm) / ynorm, "headline": False}
-            gpu_launches += args.steps * leg["roofline"]["kernel_launches_per_apply"]
-            del op2
-        except bd.BenchDolfinxError as exc:
-            variants[other] = {"value": None, "note": str(exc)}
+        others = ["precomputed" if head_mode != "precomputed" else "onthefly"]
+        if head_mode == "onthefly-brick":
+            others.append("onthefly-full")   # the general parallelepiped kernel on the same mesh
+        for other in others:
+            try:
+                op2 = bd.MatFreeLaplacianGPU(mesh, degree, qmode, 2.0, dtype=dtype, halo=halo, geometry=other)
+                leg = action_leg(ctx, bd, mesh, op2, u, y, args.steps, args.warmup, degree, qmode, args.float)
+                yn2 = bd.norm(y, mesh.ndofs_owned, comm)
+                cg2 = None if args.no_cg else cg_leg(ctx, bd, mesh, op2, u, args.steps, args.warmup,
+                                                     leg["roofline"]["algorithmic_bytes_per_apply"], tsize)
+                variants[leg["geometry"]] = {"value": leg["value"], "ms_per_step": leg["ms_per_step"],
+                                             "roofline": leg["roofline"], "cg": cg2 and cg2["value"], "y_norm": yn2,
+                                             "halo": leg["halo"],
+                                             "rel_diff_y_norm_vs_headline": abs(yn2 - ynorm) / ynorm, "headline": False}
+                gpu_launches += args.steps * leg["roofline"]["kernel_launches_per_apply"]
+                del op2
+            except bd.BenchDolfinxError as exc:
+                variants[other] = {"value": None, "note": str(exc)}
 
     # ---- the GPU at qmode 0, beside the qmode-0 CPU baseline
     gpu_q0 = None
@@ -722,14 +728,18 @@ def main():
                                                    leg["roofline"]["algorithmic_bytes_per_apply"], 8)}
         gpu_launches += args.steps * leg["roofline"]["kernel_launches_per_apply"]
         if not args.no_variants:
-            other = "precomputed" if leg["geometry"] != "precomputed" else "onthefly"
-            del op6
-            op6 = bd.MatFreeLaplacianGPU(mesh6, 6, 1, 2.0, halo=halo6, geometry=other)
-            leg2 = action_leg(ctx, bd, mesh6, op6, u6, y6, args.steps, args.warmup, 6, 1, 64)
-            q6["variants"] = {leg["geometry"]: {"value": leg["value"], "roofline_frac": leg["roofline"]["frac"]},
-                              leg2["geometry"]: {"value": leg2["value"], "ms_per_step": leg2["ms_per_step"],
-                                                 "roofline": leg2["roofline"],
-                                                 "y_norm": bd.norm(y6, mesh6.ndofs_owned, comm)}}
+            others = ["precomputed" if leg["geometry"] != "precomputed" else "onthefly"]
+            if leg["geometry"] == "onthefly-brick":
+                others.append("onthefly-full")
+            q6["variants"] = {leg["geometry"]: {"value": leg["value"], "roofline_frac": leg["roofline"]["frac"]}}
+            for other in others:
+                del op6
+                op6 = bd.MatFreeLaplacianGPU(mesh6, 6, 1, 2.0, halo=halo6, geometry=other)
+                leg2 = action_leg(ctx, bd, mesh6, op6, u6, y6, args.steps, args.warmup, 6, 1, 64)
+                q6["variants"][leg2["geometry"]] = {"value": leg2["value"], "ms_per_step": leg2["ms_per_step"],
+                                                    "roofline": leg2["roofline"],
+                                                    "y_norm": bd.norm(y6, mesh6.ndofs_owned, comm)}
+                gpu_launches += args.steps * leg2["roofline"]["kernel_launches_per_apply"]
         del op6, mesh6, halo6, u6, y6
         torch.cuda.empty_cache()
 

@@ -326,9 +326,12 @@ class MatFreeLaplacianGPU:
                  geometry: str = "auto"):
         """``geometry``: "precomputed" = G stored and streamed as the reference does
         (src/laplacian.hpp:238-272), "onthefly" = G rebuilt inside the stiffness kernel from the cell
-        vertices, "auto" (default) = on the fly when every cell is a parallelepiped, precomputed otherwise."""
-        if geometry not in ("auto", "precomputed", "onthefly"):
-            raise BenchDolfinxError(-1, "geometry must be 'auto', 'precomputed' or 'onthefly'")
+        vertices, "auto" (default) = on the fly when every cell is a parallelepiped, precomputed otherwise.
+        "auto-full" / "onthefly-full": the same, but without the diagonal-G shortcut the dof-space kernels take on
+        meshes of bricks (cells with mutually orthogonal edges, e.g. the unperturbed box)."""
+        if geometry not in ("auto", "precomputed", "onthefly", "auto-full", "onthefly-full"):
+            raise BenchDolfinxError(-1, "geometry must be 'auto', 'precomputed', 'onthefly', 'auto-full' or "
+                                        "'onthefly-full'")
         self.bits = _bits(dtype)
         self.value_type = _np_dtype(self.bits)
         self.degree, self.qmode = int(degree), int(qmode)
@@ -367,7 +370,9 @@ class MatFreeLaplacianGPU:
             d.flags = 0
             self.n_owned = getattr(mesh, "ndofs_owned", d.ndofs)
         d.flags |= {"auto": 0, "onthefly": _lib.BD_FLAG_GEOMETRY_ONTHEFLY,
-                    "precomputed": _lib.BD_FLAG_GEOMETRY_PRECOMPUTED}[geometry]
+                    "precomputed": _lib.BD_FLAG_GEOMETRY_PRECOMPUTED,
+                    "auto-full": _lib.BD_FLAG_GEOMETRY_FULL_TENSOR,
+                    "onthefly-full": _lib.BD_FLAG_GEOMETRY_ONTHEFLY | _lib.BD_FLAG_GEOMETRY_FULL_TENSOR}[geometry]
         d.phi0, d.dphi1 = _ptr(t.phi0), _ptr(t.dphi1)
         d.weights, d.dphi_geometry = _ptr(t.weights3d), _ptr(t.dphi_geometry)
         self.ndofs = int(d.ndofs)
@@ -414,10 +419,11 @@ class MatFreeLaplacianGPU:
         check(lib.bd_laplacian_apply_host_batch(self._h, halo, n, pin, pout))
 
     def geometry_mode(self):
-        """("precomputed" | "onthefly-affine" | "onthefly-general", number of non-affine cells or -1)."""
+        """("precomputed" | "onthefly-affine" | "onthefly-general" | "onthefly-brick", number of non-affine cells
+        or -1).  "onthefly-brick": every cell affine with orthogonal edges, dof-space kernel with diagonal G_cell."""
         mode, n = C.c_int(), C.c_int64()
         check(lib.bd_laplacian_geometry_mode(self._h, C.byref(mode), C.byref(n)))
-        return ("precomputed", "onthefly-affine", "onthefly-general")[mode.value], n.value
+        return ("precomputed", "onthefly-affine", "onthefly-general", "onthefly-brick")[mode.value], n.value
 
     def get_diag_inverse(self, diag_inv=None, stream=None):
         """1 / diag(A) as a device vector (MatrixOperator::get_diag_inverse, src/csr.hpp:154-162, computed

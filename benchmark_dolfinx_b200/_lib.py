@@ -16,6 +16,7 @@ BD_SUCCESS = 0
 BD_FLAG_BORROW_DEVICE_ARRAYS = 1
 BD_FLAG_GEOMETRY_ONTHEFLY = 2
 BD_FLAG_GEOMETRY_PRECOMPUTED = 4
+BD_FLAG_GEOMETRY_FULL_TENSOR = 8
 BD_UNIQUE_ID_BYTES = 128
 
 

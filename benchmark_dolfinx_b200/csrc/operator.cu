@@ -82,22 +82,23 @@ template <typename T>
 int count_nonaffine(bd_laplacian* op)
 {
   const std::int64_t n = op->n_lcells + op->n_bcells;
-  op->n_nonaffine = 0;
+  op->n_nonaffine = op->n_nonorthogonal = 0;
   if (n == 0)
     return BD_SUCCESS;
   unsigned long long* cnt = nullptr;
-  BD_CUDA_CHECK(cudaMalloc(&cnt, sizeof(unsigned long long)));
-  cudaMemset(cnt, 0, sizeof(unsigned long long));
+  BD_CUDA_CHECK(cudaMalloc(&cnt, 2 * sizeof(unsigned long long)));
+  cudaMemset(cnt, 0, 2 * sizeof(unsigned long long));
   const std::int64_t want = (n + 255) / 256;
   const std::int64_t cap = static_cast<std::int64_t>(sm_count()) * 8;
   count_nonaffine_kernel<T><<<static_cast<int>(want < cap ? want : cap), 256>>>(
       reinterpret_cast<const T*>(op->xgeom.ptr), op->geometry_dofmap.ptr, op->cell_list.ptr, n, cnt);
-  unsigned long long h = 0;
-  const cudaError_t e = cudaMemcpy(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost);
+  unsigned long long h[2] = {0, 0};
+  const cudaError_t e = cudaMemcpy(h, cnt, sizeof(h), cudaMemcpyDeviceToHost);
   cudaFree(cnt);
   if (e != cudaSuccess)
     return fail(BD_ERR_CUDA, "affine-cell count failed: %s", cudaGetErrorString(e));
-  op->n_nonaffine = static_cast<std::int64_t>(h);
+  op->n_nonaffine = static_cast<std::int64_t>(h[0]);
+  op->n_nonorthogonal = static_cast<std::int64_t>(h[1]);
   return BD_SUCCESS;
 }
 
@@ -251,6 +252,11 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
     op->geom_mode = 1;
   else
     op->geom_mode = 0;
+  // every cell a brick (orthogonal edges, any orientation -- the benchmark's own unperturbed box mesh): G_cell is
+  // diagonal and the dof-space kernels drop the three mixed terms
+  op->g_diagonal = op->geom_mode == 1 && op->n_nonorthogonal == 0 && (d->flags & BD_FLAG_GEOMETRY_FULL_TENSOR) == 0
+                   && (affine_kernel_used(op->scalar_bits, op->degree, op->is_identity)
+                       || affine_col_used(op->scalar_bits, op->degree, op->is_identity));
   // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272), written
   // straight into the layout the stiffness kernel streams; lcells and bcells are separate segments
   // because they are separate launches (the bcells pointer offset of src/laplacian.hpp:329).
@@ -331,6 +337,7 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
   a.g_layout = op->g_layout;
   a.mdofmap = op->masked_dofmap.ptr;
   a.geom_mode = op->geom_mode;
+  a.g_diagonal = op->g_diagonal;
   a.xgeom = op->xgeom.ptr;
   a.gdofmap = op->geometry_dofmap.ptr;
   a.w1d = op->w1d.data();
@@ -388,7 +395,9 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
                  ? "bd::stiffness_affine_kernel (dof-space 1-D operators M, S, C; geometry on the fly)"
                  : "bd::stiffness_slab_otf_kernel (register slabs, geometry on the fly)";
     snprintf(buf, n, "%s, T=%s, P=%d, nq=%d, %s", kernel, t, op->degree, op->nq,
-             op->geom_mode == 1 ? "all cells affine: G(q) = w_q G_cell" : "general cells: J(q) from the 8 vertices");
+             op->g_diagonal       ? "all cells bricks (orthogonal edges): G(q) = w_q diag(G_cell)"
+             : op->geom_mode == 1 ? "all cells affine: G(q) = w_q G_cell"
+                                  : "general cells: J(q) from the 8 vertices");
     return BD_SUCCESS;
   }
   snprintf(buf, n, "%s, T=%s, P=%d, nq=%d, G layout %d", kernel, t, op->degree, op->nq, op->g_layout);
@@ -398,7 +407,7 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
 extern "C" int bd_laplacian_geometry_mode(bd_laplacian* op, int* mode, int64_t* n_nonaffine)
 {
   BD_REQUIRE(op && mode && n_nonaffine, "bd_laplacian_geometry_mode: null argument");
-  *mode = op->geom_mode;
+  *mode = op->g_diagonal ? 3 : op->geom_mode;
   *n_nonaffine = op->n_nonaffine;
   return BD_SUCCESS;
 }

@@ -65,7 +65,7 @@ __device__ __forceinline__ void load_table_row(const T* __restrict__ table, int 
 
 // Unroll factor of the row loops of stiffness_affine_kernel (measured, profiles/r2_affine_ab.txt): two iterations at a time
 // in fp64 (Q3 48.4 -> 50.7 GDoF/s; four spill: 33.6), everything in fp32 and at nd = 2 (Q4 fp32 70.2 -> 76.2, Q1 16.2 -> 18.3).
-constexpr int affine_unroll(bool is_double, int nd) { return (!is_double || nd == 2) ? 4 : 2; }
+constexpr int affine_unroll(bool is_double, int nd, bool diag = false) { return (!is_double || nd == 2 || diag) ? 4 : 2; }
 struct AffineStrides
 {
   int ch, si, sj; // cells per group of the cell index, strides of i and j
@@ -126,7 +126,8 @@ constexpr AffineStrides affine_strides(int nd, bool is_double, int kch)
 
 // COMPACT: no padding at all (cell index fastest, then i, then j): the phase-B reads then have 2-way bank conflicts for
 // some nd, which costs little where the exchange is a small part of the work (column-round kernel) and buys occupancy.
-template <typename T, int P, int WARPS_, int KCH_, bool COMPACT = false>
+// NPLANES: planes exchanged between the phases (4: for S_x, M_x, C_x, C^T_x; 2 when G_cell is diagonal).
+template <typename T, int P, int WARPS_, int KCH_, bool COMPACT = false, int NPLANES = 4>
 struct AffineConfig
 {
   static constexpr int ND = P + 1;
@@ -136,24 +137,27 @@ struct AffineConfig
   static constexpr AffineStrides ST = COMPACT ? AffineStrides{32 / (P + 1), 32 / (P + 1), (P + 1) * (32 / (P + 1))}
                                               : affine_strides(ND, sizeof(T) == 8, KCH_);
   static constexpr int CH = ST.ch, SI = ST.si, SJ = ST.sj, SK = ND * SJ, HS = KCH * SK, PL = (CW / CH) * HS;
-  static constexpr int WARP_BYTES = (4 * PL * int(sizeof(T)) + 15) / 16 * 16;
+  static constexpr int WARP_BYTES = (NPLANES * PL * int(sizeof(T)) + 15) / 16 * 16;
   static constexpr int WARPS = WARPS_;
   static constexpr int THREADS = WARPS * 32;
   static constexpr int CTA_SMEM = WARPS * WARP_BYTES;
 };
 
-template <typename T, int P, int WARPS_, int MINB, int KCH>
+// DIAG: every cell has mutually orthogonal edges (bricks; the operator checks at construction), so G_cell is diagonal and
+// only  y = Gc00 S_x M_y M_z u + Gc11 M_x S_y M_z u + Gc22 M_x M_y S_z u  is left: 7 instead of 17 applications of an
+// nd x nd matrix per dof plane (14 nd^4 flop per cell), two exchanged planes instead of four.
+template <typename T, int P, int WARPS_, int MINB, int KCH, bool DIAG = false>
 __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     stiffness_affine_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ xgeom,
                             const std::int32_t* __restrict__ gdofmap, const T* __restrict__ cell_constants,
                             const std::int32_t* __restrict__ mdofmap, const std::int32_t* __restrict__ cells,
                             int ncells, const __grid_constant__ AffineTables<T, P + 1> tab)
 {
-  using AC = AffineConfig<T, P, WARPS_, KCH>;
+  using AC = AffineConfig<T, P, WARPS_, KCH, false, DIAG ? 2 : 4>;
   constexpr int ND = AC::ND, CW = AC::CW, SI = AC::SI, SJ = AC::SJ, SK = AC::SK, PL = AC::PL;
   constexpr int ND2 = ND * ND, ND3 = ND2 * ND, NDP = AffineTables<T, ND>::NDP;
   constexpr bool DEEP = sizeof(T) == 8;
-  constexpr int kAffineUnroll = affine_unroll(sizeof(T) == 8, ND);
+  constexpr int kAffineUnroll = affine_unroll(sizeof(T) == 8, ND, DIAG);
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;
@@ -259,7 +263,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     const std::int32_t cell_next2 = kb + 2 < my_batches ? cell_of(batch + 2 * warps_total) : -1;
     const T kappa_next = kb + 1 < my_batches ? kappa_of(batch + warps_total) : T(0);
 
-    const T G00 = Gc[0], G01 = Gc[1], G02 = Gc[2], G11 = Gc[3], G12 = Gc[4], G22 = Gc[5];
+    [[maybe_unused]] const T G00 = Gc[0], G01 = Gc[1], G02 = Gc[2], G11 = Gc[3], G12 = Gc[4], G22 = Gc[5];
 
     // BC masking (reference :163-169): b[dof] = u[dof], the dof contributes 0 and receives nothing
     if (cell_cur >= 0)
@@ -315,13 +319,16 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
       for (int kk = 0; kk < KCH; ++kk)
       {
         const int k1 = r * KCH + kk;
-        T mz[ND], sz[ND], cz[ND], ctz[ND]; // (M_z u, S_z u, C_z u, C^T_z u)[j][k1]
+        T mz[ND], sz[ND], cz[DIAG ? 1 : ND], ctz[DIAG ? 1 : ND]; // (M_z u, S_z u, C_z u, C^T_z u)[j][k1]
         {
-          T Mr[NDP], Sr[NDP], Cr[NDP], Ctr[NDP];
+          T Mr[NDP], Sr[NDP], Cr[DIAG ? 1 : NDP], Ctr[DIAG ? 1 : NDP];
           load_table_row<T, NDP>(tab.M, k1, Mr);
           load_table_row<T, NDP>(tab.S, k1, Sr);
-          load_table_row<T, NDP>(tab.C, k1, Cr);
-          load_table_row<T, NDP>(tab.CT, k1, Ctr);
+          if constexpr (!DIAG)
+          {
+            load_table_row<T, NDP>(tab.C, k1, Cr);
+            load_table_row<T, NDP>(tab.CT, k1, Ctr);
+          }
 #pragma unroll
           for (int j = 0; j < ND; ++j)
           {
@@ -332,41 +339,58 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
               const T v = ul[j * ND + k];
               a0 = fma(Mr[k], v, a0);
               a1 = fma(Sr[k], v, a1);
-              a2 = fma(Cr[k], v, a2);  // C_z
-              a3 = fma(Ctr[k], v, a3); // C^T_z
+              if constexpr (!DIAG)
+              {
+                a2 = fma(Cr[k], v, a2);  // C_z
+                a3 = fma(Ctr[k], v, a3); // C^T_z
+              }
             }
-            mz[j] = a0, sz[j] = a1, cz[j] = a2, ctz[j] = a3;
+            mz[j] = a0, sz[j] = a1;
+            if constexpr (!DIAG)
+              cz[j] = a2, ctz[j] = a3;
           }
         }
 #pragma unroll kAffineUnroll
         for (int j1 = 0; j1 < ND; ++j1)
         {
           T p1 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0, s6 = 0, s7 = 0;
-          T Mr[NDP], Sr[NDP], Cr[NDP], Ctr[NDP];
+          T Mr[NDP], Sr[NDP], Cr[DIAG ? 1 : NDP], Ctr[DIAG ? 1 : NDP];
           load_table_row<T, NDP>(tab.M, j1, Mr);
           load_table_row<T, NDP>(tab.S, j1, Sr);
-          load_table_row<T, NDP>(tab.C, j1, Cr);
-          load_table_row<T, NDP>(tab.CT, j1, Ctr);
+          if constexpr (!DIAG)
+          {
+            load_table_row<T, NDP>(tab.C, j1, Cr);
+            load_table_row<T, NDP>(tab.CT, j1, Ctr);
+          }
 #pragma unroll
           for (int j = 0; j < ND; ++j)
           {
-            const T Mj = Mr[j], Sj = Sr[j], Cj = Cr[j], Ctj = Ctr[j];
-            p1 = fma(Mj, mz[j], p1);                   // M_y M_z
-            s1 = fma(Sj, mz[j], s1);                   // S_y M_z
-            s2 = fma(Mj, sz[j], s2);                   // M_y S_z
-            s3 = fma(Cj, ctz[j], fma(Ctj, cz[j], s3)); // C_y C^T_z + C^T_y C_z
-            s4 = fma(Ctj, mz[j], s4);                  // C^T_y M_z
-            s5 = fma(Mj, ctz[j], s5);                  // M_y C^T_z
-            s6 = fma(Cj, mz[j], s6);                   // C_y M_z
-            s7 = fma(Mj, cz[j], s7);                   // M_y C_z
+            const T Mj = Mr[j], Sj = Sr[j];
+            p1 = fma(Mj, mz[j], p1); // M_y M_z
+            s1 = fma(Sj, mz[j], s1); // S_y M_z
+            s2 = fma(Mj, sz[j], s2); // M_y S_z
+            if constexpr (!DIAG)
+            {
+              const T Cj = Cr[j], Ctj = Ctr[j];
+              s3 = fma(Cj, ctz[j], fma(Ctj, cz[j], s3)); // C_y C^T_z + C^T_y C_z
+              s4 = fma(Ctj, mz[j], s4);                  // C^T_y M_z
+              s5 = fma(Mj, ctz[j], s5);                  // M_y C^T_z
+              s6 = fma(Cj, mz[j], s6);                   // C_y M_z
+              s7 = fma(Mj, cz[j], s7);                   // M_y C_z
+            }
           }
           if (lane_ok)
           {
             T* dst = buf + kk * SK + j1 * SJ + m * SI;
-            dst[0] = G00 * p1;                              // for S_x
-            dst[PL] = fma(G11, s1, fma(G22, s2, G12 * s3)); // for M_x
-            dst[2 * PL] = fma(G01, s4, G02 * s5);           // for C_x
-            dst[3 * PL] = fma(G01, s6, G02 * s7);           // for C^T_x
+            dst[0] = G00 * p1; // for S_x
+            if constexpr (DIAG)
+              dst[PL] = fma(G11, s1, G22 * s2); // for M_x
+            else
+            {
+              dst[PL] = fma(G11, s1, fma(G22, s2, G12 * s3)); // for M_x
+              dst[2 * PL] = fma(G01, s4, G02 * s5);           // for C_x
+              dst[3 * PL] = fma(G01, s6, G02 * s7);           // for C^T_x
+            }
           }
         }
       }
@@ -395,28 +419,36 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
 #pragma unroll kAffineUnroll
         for (int i = 0; i < ND; ++i)
         {
-          T q1[KCH], q2[KCH], q3[KCH], q4[KCH];
+          T q1[KCH], q2[KCH], q3[DIAG ? 1 : KCH], q4[DIAG ? 1 : KCH];
 #pragma unroll
           for (int kk = 0; kk < KCH; ++kk)
           {
             const T* src = buf + kk * SK + m * SJ + i * SI;
-            q1[kk] = src[0], q2[kk] = src[PL], q3[kk] = src[2 * PL], q4[kk] = src[3 * PL];
+            q1[kk] = src[0], q2[kk] = src[PL];
+            if constexpr (!DIAG)
+              q3[kk] = src[2 * PL], q4[kk] = src[3 * PL];
           }
           // column i of S, M, C and row i of C: all read as rows (S, M symmetric; CT = C transposed)
-          T Sr[NDP], Mr[NDP], Ctr[NDP], Cr[NDP];
+          T Sr[NDP], Mr[NDP], Ctr[DIAG ? 1 : NDP], Cr[DIAG ? 1 : NDP];
           load_table_row<T, NDP>(tab.S, i, Sr);
           load_table_row<T, NDP>(tab.M, i, Mr);
-          load_table_row<T, NDP>(tab.CT, i, Ctr);
-          load_table_row<T, NDP>(tab.C, i, Cr);
+          if constexpr (!DIAG)
+          {
+            load_table_row<T, NDP>(tab.CT, i, Ctr);
+            load_table_row<T, NDP>(tab.C, i, Cr);
+          }
 #pragma unroll
           for (int i1 = 0; i1 < ND; ++i1)
           {
-            const T Si = Sr[i1], Mi = Mr[i1], Ci = Ctr[i1], Cti = Cr[i1];
+            const T Si = Sr[i1], Mi = Mr[i1];
 #pragma unroll
             for (int kk = 0; kk < KCH; ++kk)
             {
               T& o = out[i1 * ND + r * KCH + kk];
-              o = fma(Si, q1[kk], fma(Mi, q2[kk], fma(Ci, q3[kk], fma(Cti, q4[kk], o))));
+              if constexpr (DIAG)
+                o = fma(Si, q1[kk], fma(Mi, q2[kk], o));
+              else
+                o = fma(Si, q1[kk], fma(Mi, q2[kk], fma(Ctr[i1], q3[kk], fma(Cr[i1], q4[kk], o))));
             }
           }
         }
@@ -427,11 +459,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
         if (sdof[t] >= 0)
-#ifdef BD_AFFINE_NOATOMIC
-          y[sdof[t]] = out[t]; // TIMING EXPERIMENT ONLY (wrong results)
-#else
           atomicAdd(y + sdof[t], out[t]); // result unused -> RED.E.ADD (reference :424-425)
-#endif
     }
     __syncwarp(); // the buffer is rewritten by the next batch's phase A
 

@@ -7,6 +7,10 @@ int launch_stiffness_affine_col_any(int scalar_bits, int degree, const Stiffness
 {
 #define BD_COL_CASE(P)                                                                             \
   case P:                                                                                          \
+    if (a.g_diagonal)                                                                              \
+      return scalar_bits == 64                                                                     \
+                 ? launch_stiffness_affine_col<double, P, P + 2, false, 1, affine_col_compact(64, P), true>(a) \
+                 : launch_stiffness_affine_col<float, P, P + 2, false, 1, affine_col_compact(32, P), true>(a); \
     return scalar_bits == 64                                                                       \
                ? launch_stiffness_affine_col<double, P, P + 2, false, 1, affine_col_compact(64, P)>(a) \
                : launch_stiffness_affine_col<float, P, P + 2, false, 1, affine_col_compact(32, P)>(a);

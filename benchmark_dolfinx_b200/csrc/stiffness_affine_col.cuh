@@ -17,13 +17,13 @@
 
 namespace bd
 {
-template <typename T, int P, int WARPS_, bool COMPACT>
+template <typename T, int P, int WARPS_, bool COMPACT, bool DIAG = false>
 struct AffineColConfig
 {
-  using X = AffineConfig<T, P, WARPS_, 1, COMPACT>; // exchange buffer of one column
+  using X = AffineConfig<T, P, WARPS_, 1, COMPACT, DIAG ? 2 : 4>; // exchange buffer of one column
   static constexpr int ND = P + 1, CW = 32 / ND, ND2 = ND * ND;
   static constexpr int U_BYTES = ND2 * 32 * int(sizeof(T));
-  static constexpr int X_BYTES = (4 * X::PL * int(sizeof(T)) + 15) / 16 * 16;
+  static constexpr int X_BYTES = X::WARP_BYTES;
   static constexpr int WARP_BYTES = U_BYTES + X_BYTES;
   static constexpr int WARPS = WARPS_;
   static constexpr int THREADS = WARPS * 32;
@@ -39,14 +39,15 @@ __device__ __forceinline__ void cp_async_scalar(T* dst_smem, const T* src)
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr(dst_smem)), "l"(src) : "memory");
 }
 
-template <typename T, int P, int WARPS_, int MINB, bool COMPACT>
+// DIAG: G_cell diagonal (cells with mutually orthogonal edges), see stiffness_affine.cuh.
+template <typename T, int P, int WARPS_, int MINB, bool COMPACT, bool DIAG = false>
 __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     stiffness_affine_col_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ xgeom,
                                 const std::int32_t* __restrict__ gdofmap, const T* __restrict__ cell_constants,
                                 const std::int32_t* __restrict__ mdofmap, const std::int32_t* __restrict__ cells,
                                 int ncells, const __grid_constant__ AffineTables<T, P + 1> tab)
 {
-  using CC = AffineColConfig<T, P, WARPS_, COMPACT>;
+  using CC = AffineColConfig<T, P, WARPS_, COMPACT, DIAG>;
   using AC = typename CC::X;
   constexpr int ND = CC::ND, CW = CC::CW, ND2 = CC::ND2, ND3 = ND2 * ND, NDP = AffineTables<T, ND>::NDP;
   constexpr int SI = AC::SI, SJ = AC::SJ, PL = AC::PL;
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
       }
       otf_cell_g(a, b, cc, kappa, Gc);
     }
-    const T G00 = Gc[0], G01 = Gc[1], G02 = Gc[2], G11 = Gc[3], G12 = Gc[4], G22 = Gc[5];
+    [[maybe_unused]] const T G00 = Gc[0], G01 = Gc[1], G02 = Gc[2], G11 = Gc[3], G12 = Gc[4], G22 = Gc[5];
 
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     // BC masking (reference :163-169): b[dof] = u[dof], the dof contributes 0 and receives nothing (rare path)
@@ -147,16 +148,23 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     {
       // z contraction of the whole plane for column k1: (M_z u, S_z u, C_z u, C^T_z u)[j][k1].  Unrolled over k: the
       // four table rows of k1 (4 nd entries) are fetched once per round.
-      T mz[ND], sz[ND], cz[ND], ctz[ND];
+      constexpr int NDX = DIAG ? 1 : ND, NDPX = DIAG ? 1 : NDP; // the C / C^T pieces do not exist with DIAG
+      T mz[ND], sz[ND], cz[NDX], ctz[NDX];
 #pragma unroll
       for (int j = 0; j < ND; ++j)
-        mz[j] = sz[j] = cz[j] = ctz[j] = 0;
+        mz[j] = sz[j] = 0;
+#pragma unroll
+      for (int j = 0; j < NDX; ++j)
+        cz[j] = ctz[j] = 0;
       {
-        T Mr[NDP], Sr[NDP], Cr[NDP], Ctr[NDP];
+        T Mr[NDP], Sr[NDP], Cr[NDPX], Ctr[NDPX];
         load_table_row<T, NDP>(tab.M, k1, Mr);
         load_table_row<T, NDP>(tab.S, k1, Sr);
-        load_table_row<T, NDP>(tab.C, k1, Cr);
-        load_table_row<T, NDP>(tab.CT, k1, Ctr);
+        if constexpr (!DIAG)
+        {
+          load_table_row<T, NDP>(tab.C, k1, Cr);
+          load_table_row<T, NDP>(tab.CT, k1, Ctr);
+        }
 #pragma unroll
         for (int k = 0; k < ND; ++k)
         {
@@ -166,8 +174,11 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
             const T v = U[(j * ND + k) * 32];
             mz[j] = fma(Mr[k], v, mz[j]);
             sz[j] = fma(Sr[k], v, sz[j]);
-            cz[j] = fma(Cr[k], v, cz[j]);
-            ctz[j] = fma(Ctr[k], v, ctz[j]);
+            if constexpr (!DIAG)
+            {
+              cz[j] = fma(Cr[k], v, cz[j]);
+              ctz[j] = fma(Ctr[k], v, ctz[j]);
+            }
           }
         }
       }
@@ -176,31 +187,43 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
       for (int j1 = 0; j1 < ND; ++j1)
       {
         T p1 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0, s6 = 0, s7 = 0;
-        T Mr[NDP], Sr[NDP], Cr[NDP], Ctr[NDP];
+        T Mr[NDP], Sr[NDP], Cr[NDPX], Ctr[NDPX];
         load_table_row<T, NDP>(tab.M, j1, Mr);
         load_table_row<T, NDP>(tab.S, j1, Sr);
-        load_table_row<T, NDP>(tab.C, j1, Cr);
-        load_table_row<T, NDP>(tab.CT, j1, Ctr);
+        if constexpr (!DIAG)
+        {
+          load_table_row<T, NDP>(tab.C, j1, Cr);
+          load_table_row<T, NDP>(tab.CT, j1, Ctr);
+        }
 #pragma unroll
         for (int j = 0; j < ND; ++j)
         {
-          const T Mj = Mr[j], Sj = Sr[j], Cj = Cr[j], Ctj = Ctr[j];
+          const T Mj = Mr[j], Sj = Sr[j];
           p1 = fma(Mj, mz[j], p1);
           s1 = fma(Sj, mz[j], s1);
           s2 = fma(Mj, sz[j], s2);
-          s3 = fma(Cj, ctz[j], fma(Ctj, cz[j], s3));
-          s4 = fma(Ctj, mz[j], s4);
-          s5 = fma(Mj, ctz[j], s5);
-          s6 = fma(Cj, mz[j], s6);
-          s7 = fma(Mj, cz[j], s7);
+          if constexpr (!DIAG)
+          {
+            const T Cj = Cr[j], Ctj = Ctr[j];
+            s3 = fma(Cj, ctz[j], fma(Ctj, cz[j], s3));
+            s4 = fma(Ctj, mz[j], s4);
+            s5 = fma(Mj, ctz[j], s5);
+            s6 = fma(Cj, mz[j], s6);
+            s7 = fma(Mj, cz[j], s7);
+          }
         }
         if (lane_ok)
         {
           T* dst = buf + j1 * SJ + m * SI;
-          dst[0] = G00 * p1;                              // for S_x
-          dst[PL] = fma(G11, s1, fma(G22, s2, G12 * s3)); // for M_x
-          dst[2 * PL] = fma(G01, s4, G02 * s5);           // for C_x
-          dst[3 * PL] = fma(G01, s6, G02 * s7);           // for C^T_x
+          dst[0] = G00 * p1; // for S_x
+          if constexpr (DIAG)
+            dst[PL] = fma(G11, s1, G22 * s2); // for M_x
+          else
+          {
+            dst[PL] = fma(G11, s1, fma(G22, s2, G12 * s3)); // for M_x
+            dst[2 * PL] = fma(G01, s4, G02 * s5);           // for C_x
+            dst[3 * PL] = fma(G01, s6, G02 * s7);           // for C^T_x
+          }
         }
       }
       __syncwarp();
@@ -224,34 +247,50 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
           for (int i1 = 0; i1 < ND; ++i1)
             sd[i1] = kBcBit;
         }
-        T oS[ND], oM[ND], oC[ND], oT[ND];
+        T oS[ND], oM[ND], oC[NDX], oT[NDX];
 #pragma unroll
         for (int i1 = 0; i1 < ND; ++i1)
-          oS[i1] = oM[i1] = oC[i1] = oT[i1] = 0;
+          oS[i1] = oM[i1] = 0;
+#pragma unroll
+        for (int i1 = 0; i1 < NDX; ++i1)
+          oC[i1] = oT[i1] = 0;
 #pragma unroll kColUnroll
         for (int i = 0; i < ND; ++i)
         {
           const T* src = buf + m * SJ + i * SI;
-          const T q1 = src[0], q2 = src[PL], q3 = src[2 * PL], q4 = src[3 * PL];
+          const T q1 = src[0], q2 = src[PL];
           // column i of S, M, C and row i of C, all read as rows (S, M symmetric; CT = C transposed)
-          T Sr[NDP], Mr[NDP], Ctr[NDP], Cr[NDP];
+          T Sr[NDP], Mr[NDP], Ctr[NDPX], Cr[NDPX];
           load_table_row<T, NDP>(tab.S, i, Sr);
           load_table_row<T, NDP>(tab.M, i, Mr);
-          load_table_row<T, NDP>(tab.CT, i, Ctr);
-          load_table_row<T, NDP>(tab.C, i, Cr);
 #pragma unroll
           for (int i1 = 0; i1 < ND; ++i1)
           {
             oS[i1] = fma(Sr[i1], q1, oS[i1]);
             oM[i1] = fma(Mr[i1], q2, oM[i1]);
-            oC[i1] = fma(Ctr[i1], q3, oC[i1]);
-            oT[i1] = fma(Cr[i1], q4, oT[i1]);
+          }
+          if constexpr (!DIAG)
+          {
+            const T q3 = src[2 * PL], q4 = src[3 * PL];
+            load_table_row<T, NDP>(tab.CT, i, Ctr);
+            load_table_row<T, NDP>(tab.C, i, Cr);
+#pragma unroll
+            for (int i1 = 0; i1 < ND; ++i1)
+            {
+              oC[i1] = fma(Ctr[i1], q3, oC[i1]);
+              oT[i1] = fma(Cr[i1], q4, oT[i1]);
+            }
           }
         }
 #pragma unroll
         for (int i1 = 0; i1 < ND; ++i1)
           if (sd[i1] >= 0)
-            atomicAdd(y + sd[i1], (oS[i1] + oM[i1]) + (oC[i1] + oT[i1])); // result unused -> RED.E.ADD (reference :424-425)
+          {
+            T o = oS[i1] + oM[i1];
+            if constexpr (!DIAG)
+              o += oC[i1] + oT[i1];
+            atomicAdd(y + sd[i1], o); // result unused -> RED.E.ADD (reference :424-425)
+          }
       }
       __syncwarp(); // the exchange buffer is rewritten by the next round
     }

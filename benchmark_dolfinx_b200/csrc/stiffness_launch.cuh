@@ -35,6 +35,7 @@ struct StiffnessArgs
   // geometry on the fly (stiffness_slab_otf.cuh, stiffness_mma8_otf.cuh): no G; 1 = every cell of the list is
   // affine (verified by the caller), 2 = general cells (affine batches still take the shortcut)
   int geom_mode = 0;
+  bool g_diagonal = false; // geom_mode 1 and every cell has orthogonal edges: G_cell is diagonal (dof-space kernels)
   const void* xgeom = nullptr;           // T [nnodes][3]
   const std::int32_t* gdofmap = nullptr; // [ncells][8], tensor-product vertex order
   const double* w1d = nullptr;           // host, [nq] 1-D quadrature weights
@@ -319,18 +320,18 @@ void fill_affine_tables(AffineTables<T, ND>& tab, const StiffnessArgs& a)
 }
 
 // Dof-space kernel for meshes of parallelepipeds (stiffness_affine.cuh), degree <= 3.
-template <typename T, int P, int NQ, bool IDENTITY, int MINB, int KCH>
+template <typename T, int P, int NQ, bool IDENTITY, int MINB, int KCH, bool DIAG = false>
 int launch_stiffness_affine(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
-  using AC = AffineConfig<T, P, 1, KCH>;
+  using AC = AffineConfig<T, P, 1, KCH, false, DIAG ? 2 : 4>;
   if (a.ncells == 0)
     return BD_SUCCESS;
   if (a.ncells > 0x7fffffffLL)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d)
     return fail(BD_ERR_INVALID_ARGUMENT, "the affine-cell kernel needs the masked dofmap, vertices and 1-D rule");
-  auto kernel = stiffness_affine_kernel<T, P, 1, MINB, KCH>;
+  auto kernel = stiffness_affine_kernel<T, P, 1, MINB, KCH, DIAG>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -356,18 +357,18 @@ int launch_stiffness_affine(const StiffnessArgs& a)
 }
 
 // Dof-space kernel with the plane in shared memory and column rounds (stiffness_affine_col.cuh), degree 4..7.
-template <typename T, int P, int NQ, bool IDENTITY, int MINB, bool COMPACT>
+template <typename T, int P, int NQ, bool IDENTITY, int MINB, bool COMPACT, bool DIAG = false>
 int launch_stiffness_affine_col(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
-  using CC = AffineColConfig<T, P, 1, COMPACT>;
+  using CC = AffineColConfig<T, P, 1, COMPACT, DIAG>;
   if (a.ncells == 0)
     return BD_SUCCESS;
   if (a.ncells > 0x7fffffffLL)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d)
     return fail(BD_ERR_INVALID_ARGUMENT, "the affine-cell kernel needs the masked dofmap, vertices and 1-D rule");
-  auto kernel = stiffness_affine_col_kernel<T, P, 1, MINB, COMPACT>;
+  auto kernel = stiffness_affine_col_kernel<T, P, 1, MINB, COMPACT, DIAG>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -400,7 +401,8 @@ int launch_stiffness_slab_otf(const StiffnessArgs& a)
     // every cell a parallelepiped: the dof-space kernel (one exchange round, uncapped registers: measured best,
     // profiles/r2_affine_ab.txt)
     if (a.geom_mode == 1)
-      return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, P + 1>(a);
+      return a.g_diagonal ? launch_stiffness_affine<T, P, NQ, IDENTITY, 1, P + 1, true>(a)
+                          : launch_stiffness_affine<T, P, NQ, IDENTITY, 1, P + 1, false>(a);
   }
   if constexpr (NQ > 6)
     return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");

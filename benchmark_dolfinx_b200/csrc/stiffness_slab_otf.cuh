@@ -564,7 +564,10 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   }
 }
 
-// Number of cells of a list that are not affine by the kernel's own criterion (setup).
+// Setup: count[0] = cells of a list that are not affine by the kernel's own criterion; count[1] = cells that are not
+// affine with mutually orthogonal edges (bricks, in any orientation), i.e. whose G_cell = kappa K K^T / det J has
+// off-diagonal entries above rounding level (8 eps of the largest diagonal entry; exactly 0 on an axis-aligned box
+// mesh).  Where count[1] = 0 the dof-space kernels drop the three mixed terms (stiffness_affine.cuh, DIAG).
 template <typename T>
 __global__ void __launch_bounds__(256)
     count_nonaffine_kernel(const T* __restrict__ xgeom, const std::int32_t* __restrict__ gdofmap,
@@ -572,7 +575,7 @@ __global__ void __launch_bounds__(256)
                            unsigned long long* __restrict__ count)
 {
   const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
-  unsigned local = 0;
+  unsigned local = 0, local_no = 0;
   for (std::int64_t i = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < ncells; i += stride)
   {
     const std::int32_t* gd = gdofmap + static_cast<std::int64_t>(cells[i]) * 8;
@@ -587,10 +590,19 @@ __global__ void __launch_bounds__(256)
     }
     TrilinearMap<T> map;
     map.from_vertices(X);
-    local += map.affine() ? 0u : 1u;
+    const bool aff = map.affine();
+    T Gc[6];
+    otf_cell_g(map.c100, map.c010, map.c001, T(1), Gc);
+    const T diag = fmax(fabs(Gc[0]), fmax(fabs(Gc[3]), fabs(Gc[5])));
+    const T off = fmax(fabs(Gc[1]), fmax(fabs(Gc[2]), fabs(Gc[4])));
+    local += aff ? 0u : 1u;
+    local_no += (aff && off <= otf_affine_eps<T>() * diag) ? 0u : 1u; // NaN (degenerate cell) counts as not orthogonal
   }
   local = __reduce_add_sync(0xffffffffu, local);
+  local_no = __reduce_add_sync(0xffffffffu, local_no);
   if ((threadIdx.x & 31) == 0 && local)
     atomicAdd(count, static_cast<unsigned long long>(local));
+  if ((threadIdx.x & 31) == 0 && local_no)
+    atomicAdd(count + 1, static_cast<unsigned long long>(local_no));
 }
 } // namespace bd

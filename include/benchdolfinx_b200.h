@@ -97,6 +97,10 @@ typedef struct bd_laplacian_desc
  * BD_ERR_UNSUPPORTED. */
 #define BD_FLAG_GEOMETRY_ONTHEFLY 2u
 #define BD_FLAG_GEOMETRY_PRECOMPUTED 4u
+/* On meshes whose cells all have mutually orthogonal edges (bricks, e.g. the benchmark's unperturbed box) G_cell is
+ * diagonal and the on-the-fly dof-space kernels skip its three off-diagonal terms.  This flag keeps the full
+ * symmetric G_cell (for A/B measurements and tests of the general parallelepiped kernel on a box mesh). */
+#define BD_FLAG_GEOMETRY_FULL_TENSOR 8u
 
 /* Constructor: copies/borrows the arrays, precomputes G over [lcells..., bcells...]
  * (compute_geometry, src/laplacian.hpp:214-224,238-272) on the current device. */
@@ -137,7 +141,8 @@ int bd_laplacian_apply_host_batch(bd_laplacian* op, struct bd_halo* halo, int nv
  * has dolfinx::common::Timer scopes around whole phases, src/laplacian_solver.cpp:90,197.) */
 int bd_laplacian_profile(bd_laplacian* op, int enable);
 /* Which geometry variant the operator uses (no counterpart in the reference, which always precomputes):
- * *mode = 0 precomputed G, 1 on the fly with every cell affine, 2 on the fly with general cells;
+ * *mode = 0 precomputed G, 1 on the fly with every cell affine, 2 on the fly with general cells, 3 on the fly with
+ * every cell a brick (affine with orthogonal edges: diagonal G_cell, dof-space kernels only);
  * *n_nonaffine = number of listed cells that are not parallelepipeds (to the rounding of their coordinates). */
 int bd_laplacian_geometry_mode(bd_laplacian* op, int* mode, int64_t* n_nonaffine);
 /* One-line description of the stiffness kernel variant this operator launches (for reports). */

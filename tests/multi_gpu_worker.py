@@ -45,7 +45,7 @@ def main():
     halo = bd.Halo(comm, mesh)
     u = mesh.assemble_rhs(1)
     norms = {}
-    for geo in ("precomputed", "onthefly"):
+    for geo in ("precomputed", "onthefly", "onthefly-full"):
         op = bd.MatFreeLaplacianGPU(mesh, 3, 1, 2.0, halo=halo, geometry=geo)
         y = torch.zeros_like(u)
         halo.profile(True)

@@ -32,14 +32,20 @@ class _Mesh:
 
 
 def _case(degree, qmode, kind):
-    """kind: box (axis-aligned), sheared (affine map of the box: parallelepipeds), perturbed (general hexahedra),
-    mixed (a few perturbed vertices in an otherwise sheared mesh)."""
+    """kind: box (axis-aligned bricks; box-full: the same mesh, diagonal-G shortcut switched off), rotated (the box
+    under a rotation: bricks only to rounding), sheared (affine map of the box: parallelepipeds), perturbed (general
+    hexahedra), mixed (a few perturbed vertices in an otherwise sheared mesh)."""
     mesh = create_box_mesh(compute_mesh_size(12000, degree), degree,
                            geom_perturb_fact=0.2 if kind == "perturbed" else 0.0)
     x = mesh.xgeom.copy()
     if kind in ("sheared", "mixed"):
         A = np.array([[1.0, 0.3, -0.2], [0.1, 0.9, 0.25], [-0.15, 0.2, 1.1]])
         x = x @ A.T + np.array([0.3, -0.1, 0.2])
+    if kind == "rotated":
+        a, b = 0.7, -0.4
+        Rz = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
+        Rx = np.array([[1, 0, 0], [0, np.cos(b), -np.sin(b)], [0, np.sin(b), np.cos(b)]])
+        x = x @ (Rz @ Rx).T + np.array([0.3, -0.1, 0.2])
     if kind == "mixed":
         rng = np.random.default_rng(7)
         h = 1.0 / max(compute_mesh_size(12000, degree))
@@ -55,6 +61,7 @@ _CACHE = {}
 
 
 def _cached(degree, qmode, kind):
+    kind = "box" if kind == "box-full" else kind
     key = (degree, qmode, kind)
     if key not in _CACHE:
         m, u, oracle = _case(degree, qmode, kind)
@@ -72,7 +79,7 @@ def grid_cap():
 _PQ = [(p, q) for p in range(1, 8) for q in (0, 1)]
 
 
-@pytest.mark.parametrize("kind", ["box", "sheared", "perturbed", "mixed"])
+@pytest.mark.parametrize("kind", ["box", "box-full", "rotated", "sheared", "perturbed", "mixed"])
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("degree,qmode", _PQ)
 def test_onthefly_matches_oracle(degree, qmode, dtype, kind, grid_cap):
@@ -84,10 +91,17 @@ def test_onthefly_matches_oracle(degree, qmode, dtype, kind, grid_cap):
         with pytest.raises(bd.BenchDolfinxError):
             bd.MatFreeLaplacianGPU(m, degree, qmode, 2.0, dtype=dtype, geometry="onthefly")
         return
-    op = bd.MatFreeLaplacianGPU(m, degree, qmode, 2.0, dtype=dtype, geometry="onthefly")
+    op = bd.MatFreeLaplacianGPU(m, degree, qmode, 2.0, dtype=dtype,
+                                geometry="onthefly-full" if kind == "box-full" else "onthefly")
     mode, nonaffine = op.geometry_mode()
-    if kind in ("box", "sheared") and dtype == np.float64:
+    if kind == "box":
+        # bricks: the dof-space kernels (qmode 1) use the diagonal of G_cell only
+        assert (mode, nonaffine) == ("onthefly-brick" if qmode == 1 else "onthefly-affine", 0)
+        assert ("bricks" in op.describe()) == (qmode == 1)
+    if kind in ("box-full", "sheared") and dtype == np.float64:
         assert (mode, nonaffine) == ("onthefly-affine", 0)
+    if kind == "rotated" and dtype == np.float64:
+        assert mode in ("onthefly-brick", "onthefly-affine") and nonaffine == 0
     if kind in ("perturbed", "mixed"):
         assert mode == "onthefly-general" and nonaffine > 0
     assert "on the fly" in op.describe()
@@ -106,7 +120,7 @@ def test_onthefly_matches_oracle(degree, qmode, dtype, kind, grid_cap):
 def test_default_choice_and_forced_modes():
     import torch
     import benchmark_dolfinx_b200 as bd
-    for kind, expect in (("box", "onthefly-affine"), ("sheared", "onthefly-affine"), ("perturbed", "precomputed")):
+    for kind, expect in (("box", "onthefly-brick"), ("sheared", "onthefly-affine"), ("perturbed", "precomputed")):
         m, u, y_ref, _ = _cached(3, 1, kind)
         op = bd.MatFreeLaplacianGPU(m, 3, 1, 2.0)
         assert op.geometry_mode()[0] == expect
@@ -121,7 +135,8 @@ def test_default_choice_and_forced_modes():
     # every degree has a dof-space kernel for parallelepipeds at qmode 1 (nq = 9 included) ...
     m7 = create_box_mesh(compute_mesh_size(3000, 7), 7)
     op7 = bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0)
-    assert op7.geometry_mode()[0] == "onthefly-affine" and "affine_col" in op7.describe()
+    assert op7.geometry_mode()[0] == "onthefly-brick" and "affine_col" in op7.describe()
+    assert bd.MatFreeLaplacianGPU(m7, 7, 1, 2.0, geometry="auto-full").geometry_mode()[0] == "onthefly-affine"
     # ... while qmode 0 keeps the quadrature-space kernels (Phi = I makes them the cheaper ones): DMMA at nq = 7
     m6 = create_box_mesh(compute_mesh_size(3000, 6), 6)
     assert "affine_col" in bd.MatFreeLaplacianGPU(m6, 6, 1, 2.0).describe()
