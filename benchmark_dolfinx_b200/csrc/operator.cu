@@ -257,6 +257,16 @@ extern "C" int bd_laplacian_create(const bd_laplacian_desc* d, bd_laplacian** ou
   op->g_diagonal = op->geom_mode == 1 && op->n_nonorthogonal == 0 && (d->flags & BD_FLAG_GEOMETRY_FULL_TENSOR) == 0
                    && (affine_kernel_used(op->scalar_bits, op->degree, op->is_identity)
                        || affine_col_used(op->scalar_bits, op->degree, op->is_identity));
+  if (op->g_diagonal && affine_kernel_used(op->scalar_bits, op->degree, op->is_identity))
+  {
+    // shared z faces of consecutive listed cells, per launch segment (batches of 32 / nd cells start at the segment)
+    const int nd = op->degree + 1;
+    TRY(op->merge_flags.alloc(static_cast<size_t>(op->n_lcells + op->n_bcells > 0 ? op->n_lcells + op->n_bcells : 1)));
+    TRY(build_merge_flags(op->n_lcells, nd, 32 / nd, op->masked_dofmap.ptr, op->cell_list.ptr, op->merge_flags.ptr,
+                          nullptr));
+    TRY(build_merge_flags(op->n_bcells, nd, 32 / nd, op->masked_dofmap.ptr, op->cell_list.ptr + op->n_lcells,
+                          op->merge_flags.ptr + op->n_lcells, nullptr));
+  }
   // Geometry precompute over the whole list (compute_geometry, src/laplacian.hpp:238-272), written
   // straight into the layout the stiffness kernel streams; lcells and bcells are separate segments
   // because they are separate launches (the bcells pointer offset of src/laplacian.hpp:329).
@@ -349,6 +359,7 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
     a.G = op->G.ptr;
     a.cell_constants = op->cell_constants.ptr;
     a.cells = op->cell_list.ptr;
+    a.merge = op->merge_flags.ptr;
     a.ncells = op->n_lcells;
   }
   else
@@ -357,6 +368,7 @@ extern "C" int bd_laplacian_apply_part(bd_laplacian* op, int part, const void* i
     a.G = op->G.ptr + static_cast<size_t>(op->g_bcells_offset) * ts;
     a.cell_constants = op->cell_constants.ptr + static_cast<size_t>(op->n_lcells) * ts;
     a.cells = op->cell_list.ptr + op->n_lcells;
+    a.merge = op->merge_flags.ptr ? op->merge_flags.ptr + op->n_lcells : nullptr;
     a.ncells = op->n_bcells;
   }
   if (!op->profile || a.ncells == 0)
@@ -391,6 +403,9 @@ extern "C" int bd_laplacian_describe(bd_laplacian* op, char* buf, size_t n)
     kernel = (op->geom_mode == 1 && affine_col_used(op->scalar_bits, op->degree, op->is_identity))
                  ? "bd::stiffness_affine_col_kernel (dof-space 1-D operators M, S, C, column rounds; geometry on the fly)"
              : op->nq >= 7 ? "bd::stiffness_mma8_otf_kernel (fp64 DMMA m8n8k4 arithmetic, geometry on the fly)"
+             : (op->g_diagonal && op->degree == 3 && affine_kernel_used(op->scalar_bits, op->degree, op->is_identity))
+                 ? "bd::stiffness_affine_pipe_kernel (dof-space 1-D operators M, S; asynchronous gather, shared faces "
+                   "merged; geometry on the fly)"
              : (op->geom_mode == 1 && affine_kernel_used(op->scalar_bits, op->degree, op->is_identity))
                  ? "bd::stiffness_affine_kernel (dof-space 1-D operators M, S, C; geometry on the fly)"
                  : "bd::stiffness_slab_otf_kernel (register slabs, geometry on the fly)";

@@ -44,6 +44,7 @@ struct bd_laplacian
   int geom_mode = 0;
   std::int64_t n_nonaffine = -1;      // cells of [lcells, bcells] that are not parallelepipeds (-1: not counted)
   std::int64_t n_nonorthogonal = -1;  // ... that are not parallelepipeds with mutually orthogonal edges (bricks)
+  bd::DeviceArray<std::int8_t> merge_flags; // per list position, see build_merge_flags (dof-space pipe kernel)
   bool g_diagonal = false;            // geom_mode 1, n_nonorthogonal == 0 and a dof-space kernel serves this configuration
   std::vector<double> w1d, pts1d;     // 1-D rule recovered from weights / dphi_geometry (empty: not tensor-product)
   std::int64_t g_cell_stride() const { return 6ll * nq * nq * nq; }

@@ -48,6 +48,41 @@ int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::i
   return BD_SUCCESS;
 }
 
+// flags[p] = 1 when the cells at positions p and p + 1 of the list are in the same batch of `cw` cells and the whole
+// face k = nd - 1 of the first coincides, dof by dof (BC bit included), with the face k = 0 of the second.
+__global__ void __launch_bounds__(256)
+    merge_flags_kernel(std::int64_t ncells, int nd, int cw, const std::int32_t* __restrict__ mdofmap,
+                       const std::int32_t* __restrict__ cells, std::int8_t* __restrict__ flags)
+{
+  const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
+  const int nd2 = nd * nd, nd3 = nd2 * nd;
+  for (std::int64_t p = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; p < ncells; p += stride)
+  {
+    bool same = p + 1 < ncells && (p % cw) != cw - 1;
+    if (same)
+    {
+      const std::int32_t* ra = mdofmap + static_cast<std::int64_t>(cells[p]) * nd3;
+      const std::int32_t* rb = mdofmap + static_cast<std::int64_t>(cells[p + 1]) * nd3;
+      for (int ij = 0; ij < nd2 && same; ++ij)
+        same = ra[ij * nd + nd - 1] == rb[ij * nd];
+    }
+    flags[p] = same ? 1 : 0;
+  }
+}
+
+int build_merge_flags(std::int64_t ncells, int nd, int cw, const std::int32_t* mdofmap, const std::int32_t* cells,
+                      std::int8_t* flags, cudaStream_t stream)
+{
+  if (ncells == 0)
+    return BD_SUCCESS;
+  const std::int64_t want = (ncells + 255) / 256;
+  const std::int64_t cap = static_cast<std::int64_t>(sm_count()) * 8;
+  merge_flags_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, stream>>>(ncells, nd, cw, mdofmap, cells,
+                                                                                   flags);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
 int preferred_g_layout(int scalar_bits, int degree, int nq)
 {
   // pencil kernel (reference layout): see pencil_instantiated() in stiffness_launch.cuh

@@ -146,7 +146,9 @@ struct AffineConfig
 // DIAG: every cell has mutually orthogonal edges (bricks; the operator checks at construction), so G_cell is diagonal and
 // only  y = Gc00 S_x M_y M_z u + Gc11 M_x S_y M_z u + Gc22 M_x M_y S_z u  is left: 7 instead of 17 applications of an
 // nd x nd matrix per dof plane (14 nd^4 flop per cell), two exchanged planes instead of four.
-template <typename T, int P, int WARPS_, int MINB, int KCH, bool DIAG = false>
+// SDOF_EARLY: the scatter indices are requested at the top of the batch instead of between the phases (with DIAG phase
+// B is too short to cover them: Q3 fp64 62.9 -> 69.3 GDoF/s).
+template <typename T, int P, int WARPS_, int MINB, int KCH, bool DIAG = false, bool SDOF_EARLY = false>
 __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     stiffness_affine_kernel(const T* __restrict__ u, T* __restrict__ y, const T* __restrict__ xgeom,
                             const std::int32_t* __restrict__ gdofmap, const T* __restrict__ cell_constants,
@@ -168,6 +170,9 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   T* buf = reinterpret_cast<T*>(smem_raw + warp * AC::WARP_BYTES)
            + (lane_ok ? (c / AC::CH) * AC::HS + (c % AC::CH) : 0);
 
+  // The output pointer as a computed register value (ncells is never negative): left to itself ptxas re-reads the
+  // parameter from the constant bank before every atomic (nd^2 LDC per batch on the long scoreboard).
+  T* yy = y + (static_cast<unsigned>(ncells) >> 31);
   const int nbatches = (ncells + CW - 1) / CW;
   const int warps_total = gridDim.x * AC::WARPS;
   const int first = blockIdx.x * AC::WARPS + warp;
@@ -242,6 +247,9 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   T ul[ND2];
   std::int32_t cell_cur = my_batches > 0 ? cell_of(first) : -1;
   std::int32_t cell_next = my_batches > 1 ? cell_of(first + warps_total) : -1;
+  // DEEP: the cell index itself is requested three batches ahead -- it heads the chain cell -> dofmap row -> values, and
+  // read where it is needed its latency is exposed once per batch (18.6 % of the stall samples of the diagonal-G kernel)
+  [[maybe_unused]] std::int32_t cell_next2_reg = (DEEP && my_batches > 2) ? cell_of(first + 2 * warps_total) : -1;
   T kappa = my_batches > 0 ? kappa_of(first) : T(0);
   load_vertex_ids(cell_cur, vid);
   load_dofs(cell_cur, dof);
@@ -260,7 +268,14 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   for (int kb = 0; kb < my_batches; ++kb)
   {
     const int batch = first + kb * warps_total;
-    const std::int32_t cell_next2 = kb + 2 < my_batches ? cell_of(batch + 2 * warps_total) : -1;
+    std::int32_t cell_next2, cell_next3 = -1;
+    if constexpr (DEEP)
+    {
+      cell_next2 = cell_next2_reg;
+      cell_next3 = kb + 3 < my_batches ? cell_of(batch + 3 * warps_total) : -1;
+    }
+    else
+      cell_next2 = kb + 2 < my_batches ? cell_of(batch + 2 * warps_total) : -1;
     const T kappa_next = kb + 1 < my_batches ? kappa_of(batch + warps_total) : T(0);
 
     [[maybe_unused]] const T G00 = Gc[0], G01 = Gc[1], G02 = Gc[2], G11 = Gc[3], G12 = Gc[4], G22 = Gc[5];
@@ -310,6 +325,15 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     for (int t = 0; t < ND2; ++t)
       out[t] = 0;
     std::int32_t sdof[ND2]; // scatter indices of phase B, [i1][k]
+    if constexpr (SDOF_EARLY)
+    {
+      const std::int32_t* row = cell_cur >= 0 ? mdofmap + static_cast<std::int64_t>(cell_cur) * ND3 + m * ND : nullptr;
+#pragma unroll
+      for (int i1 = 0; i1 < ND; ++i1)
+#pragma unroll
+        for (int k = 0; k < ND; ++k)
+          sdof[i1 * ND + k] = row ? row[i1 * ND2 + k] : kBcBit;
+    }
 #pragma unroll
     for (int r = 0; r < ND / KCH; ++r)
     {
@@ -405,12 +429,16 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
           load_values(cell_next, ndof, nul);
           load_vertices(vid, Xn);
         }
-        const std::int32_t* row = cell_cur >= 0 ? mdofmap + static_cast<std::int64_t>(cell_cur) * ND3 + m * ND : nullptr;
+        if constexpr (!SDOF_EARLY)
+        {
+          const std::int32_t* row =
+              cell_cur >= 0 ? mdofmap + static_cast<std::int64_t>(cell_cur) * ND3 + m * ND : nullptr;
 #pragma unroll
-        for (int i1 = 0; i1 < ND; ++i1)
+          for (int i1 = 0; i1 < ND; ++i1)
 #pragma unroll
-          for (int k = 0; k < ND; ++k)
-            sdof[i1 * ND + k] = row ? row[i1 * ND2 + k] : kBcBit;
+            for (int k = 0; k < ND; ++k)
+              sdof[i1 * ND + k] = row ? row[i1 * ND2 + k] : kBcBit;
+        }
       }
 
       // Phase B: x contraction for the column j = m and the round's k columns (loop over the input plane i rolled)
@@ -456,10 +484,12 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     }
     if (lane_ok)
     {
+      // A constrained dof receives nothing (reference :424-425): it is sent +0.0 instead, so that the scatter is nd^2
+      // unconditional REDs -- written as `if (d >= 0) atomicAdd(...)` each one is its own branch region (BSSY / BRA
+      // / RED / BSYNC).  Constrained dofs are boundary dofs: few, and y[d] + 0.0 = y[d].
 #pragma unroll
       for (int t = 0; t < ND2; ++t)
-        if (sdof[t] >= 0)
-          atomicAdd(y + sdof[t], out[t]); // result unused -> RED.E.ADD (reference :424-425)
+        atomicAdd(yy + (sdof[t] & 0x7fffffff), sdof[t] < 0 ? T(0) : out[t]);
     }
     __syncwarp(); // the buffer is rewritten by the next batch's phase A
 
@@ -473,6 +503,7 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
     }
     cell_cur = cell_next;
     cell_next = cell_next2;
+    cell_next2_reg = cell_next3;
     kappa = kappa_next;
     cell_g(Xn, kappa, Gc);
   }

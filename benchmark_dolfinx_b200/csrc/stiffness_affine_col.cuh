@@ -65,14 +65,21 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   T* buf = reinterpret_cast<T*>(smem_raw + warp * CC::WARP_BYTES + CC::U_BYTES)
            + (lane_ok ? (c / AC::CH) * AC::HS + (c % AC::CH) : 0);
 
+  T* yy = y + (static_cast<unsigned>(ncells) >> 31); // computed register value, see stiffness_affine.cuh
   const int nbatches = (ncells + CW - 1) / CW;
   const int warps_total = gridDim.x * CC::WARPS;
   const int first = blockIdx.x * CC::WARPS + warp;
 
+  // the cell index heads the chain cell -> dofmap row -> values: requested one batch ahead
+  std::int32_t cell_ahead = (lane_ok && first < nbatches && first * CW + c < ncells) ? cells[first * CW + c] : -1;
   for (int batch = first; batch < nbatches; batch += warps_total)
   {
     const int pos = batch * CW + c;
-    const std::int32_t cell = (lane_ok && pos < ncells) ? cells[pos] : -1;
+    const std::int32_t cell = cell_ahead;
+    {
+      const int nb = batch + warps_total, npos = nb * CW + c;
+      cell_ahead = (lane_ok && nb < nbatches && npos < ncells) ? cells[npos] : -1;
+    }
     const T kappa = cell >= 0 ? cell_constants[pos] : T(0);
     const std::int32_t* row = cell >= 0 ? mdofmap + static_cast<std::int64_t>(cell) * ND3 : nullptr;
 
@@ -95,6 +102,17 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
         U[t * 32] = T(0);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
+    // the next batch's part of the dofmap row and its vertex ids towards L2 (no register, no scoreboard): their
+    // loads at the top of the next batch then find them on chip
+    if (cell_ahead >= 0)
+    {
+      const char* nrow = reinterpret_cast<const char*>(mdofmap + static_cast<std::int64_t>(cell_ahead) * ND3 + m * ND2);
+#pragma unroll
+      for (int b = 0; b < ND2 * 4 + 127; b += 128)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(nrow + (b < ND2 * 4 ? b : ND2 * 4 - 4)));
+      if (m == 0)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(gdofmap + static_cast<std::int64_t>(cell_ahead) * 8));
+    }
 
     // ---- geometry: Gc = kappa K K^T / det J from three edge vectors (lanes without a cell: unit cube)
     T Gc[6];
@@ -282,15 +300,16 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
             }
           }
         }
+        // a constrained dof receives nothing (reference :424-425): it is sent +0.0, so that the scatter is nd
+        // unconditional REDs instead of nd branch regions (see stiffness_affine.cuh)
 #pragma unroll
         for (int i1 = 0; i1 < ND; ++i1)
-          if (sd[i1] >= 0)
-          {
-            T o = oS[i1] + oM[i1];
-            if constexpr (!DIAG)
-              o += oC[i1] + oT[i1];
-            atomicAdd(y + sd[i1], o); // result unused -> RED.E.ADD (reference :424-425)
-          }
+        {
+          T o = oS[i1] + oM[i1];
+          if constexpr (!DIAG)
+            o += oC[i1] + oT[i1];
+          atomicAdd(yy + (sd[i1] & 0x7fffffff), sd[i1] < 0 ? T(0) : o);
+        }
       }
       __syncwarp(); // the exchange buffer is rewritten by the next round
     }

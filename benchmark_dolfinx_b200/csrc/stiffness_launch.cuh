@@ -8,7 +8,7 @@
 #include "stiffness_pencil_bulk.cuh"
 #include "stiffness_slab_otf.cuh"
 #include "stiffness_affine.cuh"
-#include "stiffness_affine_col.cuh"
+#include "stiffness_affine_pipe.cuh"
 
 namespace bd
 {
@@ -35,6 +35,7 @@ struct StiffnessArgs
   // geometry on the fly (stiffness_slab_otf.cuh, stiffness_mma8_otf.cuh): no G; 1 = every cell of the list is
   // affine (verified by the caller), 2 = general cells (affine batches still take the shortcut)
   int geom_mode = 0;
+  const std::int8_t* merge = nullptr; // per list position: face shared with the next listed cell (build_merge_flags)
   bool g_diagonal = false; // geom_mode 1 and every cell has orthogonal edges: G_cell is diagonal (dof-space kernels)
   const void* xgeom = nullptr;           // T [nnodes][3]
   const std::int32_t* gdofmap = nullptr; // [ncells][8], tensor-product vertex order
@@ -320,7 +321,7 @@ void fill_affine_tables(AffineTables<T, ND>& tab, const StiffnessArgs& a)
 }
 
 // Dof-space kernel for meshes of parallelepipeds (stiffness_affine.cuh), degree <= 3.
-template <typename T, int P, int NQ, bool IDENTITY, int MINB, int KCH, bool DIAG = false>
+template <typename T, int P, int NQ, bool IDENTITY, int MINB, int KCH, bool DIAG = false, bool SE = false>
 int launch_stiffness_affine(const StiffnessArgs& a)
 {
   constexpr int ND = P + 1;
@@ -331,7 +332,7 @@ int launch_stiffness_affine(const StiffnessArgs& a)
     return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
   if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d)
     return fail(BD_ERR_INVALID_ARGUMENT, "the affine-cell kernel needs the masked dofmap, vertices and 1-D rule");
-  auto kernel = stiffness_affine_kernel<T, P, 1, MINB, KCH, DIAG>;
+  auto kernel = stiffness_affine_kernel<T, P, 1, MINB, KCH, DIAG, SE>;
   static thread_local int blocks_per_sm[64] = {0};
   int dev = 0;
   BD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -352,6 +353,43 @@ int launch_stiffness_affine(const StiffnessArgs& a)
   kernel<<<grid, AC::THREADS, AC::CTA_SMEM, a.stream>>>(
       static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.xgeom), a.gdofmap,
       static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, static_cast<int>(a.ncells), tab);
+  BD_CUDA_CHECK(cudaGetLastError());
+  return BD_SUCCESS;
+}
+
+// Dof-space kernel with the asynchronous gather pipeline (stiffness_affine_pipe.cuh).
+template <typename T, int P, int NQ, bool IDENTITY, int MINB, bool DIAG, int KCH>
+int launch_stiffness_affine_pipe(const StiffnessArgs& a)
+{
+  constexpr int ND = P + 1;
+  using PC = AffinePipeConfig<T, P, 1, DIAG, KCH>;
+  if (a.ncells == 0)
+    return BD_SUCCESS;
+  if (a.ncells > 0x7fffffffLL)
+    return fail(BD_ERR_INVALID_ARGUMENT, "cell list of %lld entries exceeds int32", (long long)a.ncells);
+  if (!a.mdofmap || !a.xgeom || !a.gdofmap || !a.w1d)
+    return fail(BD_ERR_INVALID_ARGUMENT, "the affine-cell kernel needs the masked dofmap, vertices and 1-D rule");
+  auto kernel = stiffness_affine_pipe_kernel<T, P, 1, MINB, DIAG, KCH>;
+  static thread_local int blocks_per_sm[64] = {0};
+  int dev = 0;
+  BD_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return fail(BD_ERR_INVALID_ARGUMENT, "device ordinal %d out of range", dev);
+  if (blocks_per_sm[dev] == 0)
+  {
+    BD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PC::CTA_SMEM));
+    int nb = 0;
+    BD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, PC::THREADS, PC::CTA_SMEM));
+    blocks_per_sm[dev] = nb > 0 ? nb : 1;
+  }
+  AffineTables<T, ND> tab;
+  fill_affine_tables<T, ND, NQ, IDENTITY>(tab, a);
+  const std::int64_t nbatches = (a.ncells + PC::CW - 1) / PC::CW;
+  const std::int64_t max_grid = static_cast<std::int64_t>(sm_count()) * blocks_per_sm[dev];
+  const int grid = static_cast<int>(clamp_grid(nbatches, max_grid));
+  kernel<<<grid, PC::THREADS, PC::CTA_SMEM, a.stream>>>(
+      static_cast<const T*>(a.u), static_cast<T*>(a.y), static_cast<const T*>(a.xgeom), a.gdofmap,
+      static_cast<const T*>(a.cell_constants), a.mdofmap, a.cells, a.merge, static_cast<int>(a.ncells), tab);
   BD_CUDA_CHECK(cudaGetLastError());
   return BD_SUCCESS;
 }
@@ -401,8 +439,23 @@ int launch_stiffness_slab_otf(const StiffnessArgs& a)
     // every cell a parallelepiped: the dof-space kernel (one exchange round, uncapped registers: measured best,
     // profiles/r2_affine_ab.txt)
     if (a.geom_mode == 1)
-      return a.g_diagonal ? launch_stiffness_affine<T, P, NQ, IDENTITY, 1, P + 1, true>(a)
-                          : launch_stiffness_affine<T, P, NQ, IDENTITY, 1, P + 1, false>(a);
+    {
+      if (a.g_diagonal)
+      {
+        // bricks.  nd = 4: the asynchronous-gather kernel with merged shared faces (fp64: one exchange column per
+        // round and <= 128 registers = 16 warps/SM, 78.9 GDoF/s against 69.9 with the register pipeline; fp32: whole
+        // planes, 118.7 against 92.4).  Other nd: the register pipeline (the 4-byte index copies of the asynchronous
+        // one lose there: Q2 fp64 50.4 vs 65.6), at degree 4 / fp32 capped to 128 registers (118.5 vs 107.9).
+        // profiles/r2_brick_ab.txt
+        if constexpr (P == 3 && sizeof(T) == 8)
+          return launch_stiffness_affine_pipe<T, P, NQ, IDENTITY, 16, true, 1>(a);
+        else if constexpr (P == 3)
+          return launch_stiffness_affine_pipe<T, P, NQ, IDENTITY, 1, true, P + 1>(a);
+        else
+          return launch_stiffness_affine<T, P, NQ, IDENTITY, (P == 4 ? 16 : 1), P + 1, true, true>(a);
+      }
+      return launch_stiffness_affine<T, P, NQ, IDENTITY, 1, P + 1, false>(a);
+    }
   }
   if constexpr (NQ > 6)
     return fail(BD_ERR_UNSUPPORTED, "on-the-fly geometry: the slab kernel covers nq <= 6");
@@ -616,6 +669,9 @@ int preferred_g_layout(int scalar_bits, int degree, int nq);
 std::int64_t g_layout_size(int layout, int nq, std::int64_t ncells);
 // in stiffness_mma8.cu
 int launch_stiffness_mma8(int scalar_bits, int degree, bool identity, const StiffnessArgs& a);
+// in stiffness.cu: which consecutive cells of a list (in batches of cw) share their k = nd - 1 / k = 0 faces
+int build_merge_flags(std::int64_t ncells, int nd, int cw, const std::int32_t* mdofmap, const std::int32_t* cells,
+                      std::int8_t* flags, cudaStream_t stream);
 // in stiffness.cu: out[i] = dofmap[i] | (bc[dofmap[i]] ? 0x80000000 : 0)
 int build_masked_dofmap(std::int64_t n, const std::int32_t* dofmap, const std::int8_t* bc,
                         std::int32_t* out, cudaStream_t stream);

@@ -1,8 +1,6 @@
-// Experimental fp32 variant of the pencil kernel (stiffness_pencil.cuh) for quadrature sizes whose
-// per-cell G block is a multiple of 16 bytes (nq = 8: 12 288 B).  Selected with BD_PENCIL_BULK=1.
-// Written after the round's GPU budget was spent: it compiles (128 registers, no spills) but has NOT
-// run on a GPU yet; its parity test (tests/test_gpu_pencil_bulk.py) only runs with BD_EXPERIMENTAL=1.
-// See DESIGN.md section 8.
+// fp32 variant of the pencil kernel (stiffness_pencil.cuh) for quadrature sizes whose per-cell G block is a multiple
+// of 16 bytes (nq = 8: 12 288 B): the stored-G kernel for Q6 qmode 1 fp32 (42.6 -> 50.3 GDoF/s against the plain pencil
+// kernel, profiles/r2_experiments_ab.txt; parity in tests/test_gpu_operator.py like every other kernel).
 //
 // Two things differ from stiffness_pencil_kernel<float, ...>, both taken from the ncu source page of
 // that kernel at Q6 fp32 (profiles/r1_pencil_final_ncu_*_q6f32.*: 24 % of the stall samples are long

@@ -124,6 +124,8 @@ def test_default_choice_and_forced_modes():
         m, u, y_ref, _ = _cached(3, 1, kind)
         op = bd.MatFreeLaplacianGPU(m, 3, 1, 2.0)
         assert op.geometry_mode()[0] == expect
+        if kind == "box":
+            assert "affine_pipe" in op.describe()   # nd = 4 bricks: asynchronous gather, merged faces
         pre = bd.MatFreeLaplacianGPU(m, 3, 1, 2.0, geometry="precomputed")
         assert pre.geometry_mode()[0] == "precomputed"
         ud = torch.from_numpy(u).cuda()
