@@ -2,7 +2,7 @@
 //
 // Same algorithm and update order (unpreconditioned, `max_iter` iterations when rtol == 0).
 // What changes is where things live: every scalar (r.r, p.Ap, alpha, beta) stays in device
-// memory, the vector passes are fused (11 scalars of traffic per dof and iteration instead of
+// memory, the vector passes are fused (10 scalars of traffic per dof and iteration instead of
 // the reference's 13 + a fill), and nothing synchronises with the host, so the whole solve is
 // one asynchronous stream of kernels (+ one NCCL allreduce of a double per dot product and one
 // forward scatter per operator application on more than one rank; the reference scatters twice,
@@ -36,21 +36,20 @@ __global__ void __launch_bounds__(kVecBlock)
     partials[blockIdx.x] = s;
 }
 
-// alpha = rnorm / pAp ; x += alpha p ; r -= alpha y ; partial(r.r)     (src/cg.hpp:145-154)
+// alpha = rnorm / pAp ; r -= alpha y ; partial(r.r)                    (src/cg.hpp:145,150-154)
+// The other half of the reference's update, x += alpha p (:147), only needs the old p: it rides on the pass that
+// replaces p (cg_direction_kernel), which saves one read of p per iteration.  Same operations on the same operands.
 template <typename T>
 __global__ void __launch_bounds__(kVecBlock)
     cg_update_kernel(std::int64_t n, const double* __restrict__ rnorm, const double* __restrict__ pAp,
-                     const T* __restrict__ p, const T* __restrict__ y, T* __restrict__ x,
-                     T* __restrict__ r, double* __restrict__ partials)
+                     const T* __restrict__ y, T* __restrict__ r, double* __restrict__ partials)
 {
-  const T alpha = static_cast<T>(*rnorm / *pAp);
-  const T malpha = -alpha;
+  const T malpha = -static_cast<T>(*rnorm / *pAp);
   const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
   double s = 0;
   for (std::int64_t i = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
        i += stride)
   {
-    x[i] = p[i] * alpha + x[i];
     const T ri = y[i] * malpha + r[i];
     r[i] = ri;
     s += static_cast<double>(ri) * static_cast<double>(ri);
@@ -60,17 +59,25 @@ __global__ void __launch_bounds__(kVecBlock)
     partials[blockIdx.x] = s;
 }
 
-// beta = rnorm_new / rnorm ; p = beta p + r                              (src/cg.hpp:156,166)
-template <typename T>
+// x += alpha p (src/cg.hpp:147) ; beta = rnorm_new / rnorm ; p = beta p + r   (src/cg.hpp:156,166)
+// UPDATE_P = false: only the x update (the iteration that leaves the loop on the tolerance, :162-163)
+template <typename T, bool UPDATE_P>
 __global__ void __launch_bounds__(kVecBlock)
-    cg_direction_kernel(std::int64_t n, const double* __restrict__ rnorm_new,
-                        const double* __restrict__ rnorm, const T* __restrict__ r, T* __restrict__ p)
+    cg_direction_kernel(std::int64_t n, const double* __restrict__ rnorm_new, const double* __restrict__ rnorm,
+                        const double* __restrict__ pAp, const T* __restrict__ r, T* __restrict__ p,
+                        T* __restrict__ x)
 {
+  const T alpha = static_cast<T>(*rnorm / *pAp);
   const T beta = static_cast<T>(*rnorm_new / *rnorm);
   const std::int64_t stride = static_cast<std::int64_t>(gridDim.x) * blockDim.x;
   for (std::int64_t i = static_cast<std::int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
        i += stride)
-    p[i] = p[i] * beta + r[i];
+  {
+    const T pi = p[i];
+    x[i] = pi * alpha + x[i];
+    if constexpr (UPDATE_P)
+      p[i] = pi * beta + r[i];
+  }
 }
 
 template <typename T>
@@ -114,7 +121,7 @@ int cg_impl(bd_laplacian* op, bd_halo* halo, bd_comm* comm, T* x, const T* b, in
     // p.y
     BD_CHECK(bd_dot(op->scalar_bits, n, p, y, scal + 2, partials, s));
     BD_CHECK(allreduce_sum_f64(comm, scal + 2, 1, stream));
-    cg_update_kernel<T><<<grid, kVecBlock, 0, stream>>>(n, scal + cur, scal + 2, p, y, x, r, partials);
+    cg_update_kernel<T><<<grid, kVecBlock, 0, stream>>>(n, scal + cur, scal + 2, y, r, partials);
     BD_CUDA_CHECK(cudaGetLastError());
     BD_CHECK(launch_reduce_partials(grid, partials, scal + (cur ^ 1), stream));
     BD_CHECK(allreduce_sum_f64(comm, scal + (cur ^ 1), 1, stream));
@@ -125,9 +132,14 @@ int cg_impl(bd_laplacian* op, bd_halo* halo, bd_comm* comm, T* x, const T* b, in
       BD_CUDA_CHECK(cudaMemcpyAsync(h, scal, sizeof(h), cudaMemcpyDeviceToHost, stream));
       BD_CUDA_CHECK(cudaStreamSynchronize(stream));
       if (h[cur ^ 1] / h[3] < rtol2)
+      {
+        cg_direction_kernel<T, false><<<grid, kVecBlock, 0, stream>>>(n, scal + (cur ^ 1), scal + cur, scal + 2, r,
+                                                                     p, x);
+        BD_CUDA_CHECK(cudaGetLastError());
         break;
+      }
     }
-    cg_direction_kernel<T><<<grid, kVecBlock, 0, stream>>>(n, scal + (cur ^ 1), scal + cur, r, p);
+    cg_direction_kernel<T, true><<<grid, kVecBlock, 0, stream>>>(n, scal + (cur ^ 1), scal + cur, scal + 2, r, p, x);
     BD_CUDA_CHECK(cudaGetLastError());
     cur ^= 1;
   }
