@@ -52,8 +52,9 @@ __global__ void __launch_bounds__(WARPS_ * 32, MINB)
   constexpr int ND = CC::ND, CW = CC::CW, ND2 = CC::ND2, ND3 = ND2 * ND, NDP = AffineTables<T, ND>::NDP;
   constexpr int SI = AC::SI, SJ = AC::SJ, PL = AC::PL;
   // row loops four iterations at a time (measured: fp64 Q6 35.4 / 38.6 / 40.3 / 40.6 GDoF/s with 1 / 2 / 4 / all, but all
-  // spills at nd = 8 and loses at nd = 5, 6; profiles/r2_affine_col_ab.txt)
-  constexpr int kColUnroll = 4;
+  // spills at nd = 8 and loses at nd = 5, 6; profiles/r2_affine_col_ab.txt); with DIAG in fp64 at nd = 6, 7 all of them
+  // (Q5 61.8 -> 63.7, Q6 53.2 -> 56.5; nd = 5: 62.3 -> 60.8 and fp32 unchanged or worse; profiles/r2_brick_ab.txt)
+  constexpr int kColUnroll = (DIAG && sizeof(T) == 8 && (ND == 6 || ND == 7)) ? ND : 4;
   extern __shared__ __align__(128) unsigned char smem_raw[];
 
   const int lane = threadIdx.x & 31;
