@@ -449,11 +449,14 @@ def action_leg(ctx, bd, mesh, op, u, y, steps, warmup, degree, qmode, bits, samp
                   "note": "achieved = algorithmic flops of the kernel's algorithm (SURVEY.md section 8d for the "
                           "quadrature-space kernels, 34 nd^4 per cell for the dof-space kernel) / kernel time; the "
                           "kernels execute somewhat more (idle lanes, padding, index arithmetic)"}
-    if mode == "precomputed" or fp is None:
+    # element contributions scattered per second (one RED each unless two cells' shared face was merged first): the
+    # third ceiling of the on-the-fly kernels (measured limit on this part: about 200 G/s for fp64)
+    common["scatter_adds_per_second_g"] = (degree + 1) ** 3 * mesh.ncells / kernel_s / 1e9
+    if mode == "precomputed" or fp is None or hbm["frac"] >= fp["frac"]:
+        # stored G: the G stream bounds the kernel; on the fly: whichever ceiling is nearer leads, the other is kept
         roofline = dict(hbm, **common)
         roofline["fp64"] = fp
     else:
-        # geometry on the fly: no G stream; the fp64 pipe, not HBM, bounds the kernel
         roofline = dict(fp, **common)
         roofline["hbm"] = hbm
     return {"value": mesh.ndofs_global * steps / (1e9 * secs), "ms_per_step": 1e3 * secs / steps, "secs": secs,
