@@ -169,3 +169,34 @@ def test_onthefly_cg_and_csr_check():
     A.apply(bd_, z)
     torch.cuda.synchronize()
     assert _rel(y.cpu().numpy(), z.cpu().numpy()) < 1e-12
+
+
+@pytest.mark.parametrize("order", ["reversed", "shuffled", "split"])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_brick_kernel_with_reordered_cell_lists(order, dtype, grid_cap):
+    """The brick kernel at nd = 4 merges the faces that consecutive cells of the list share (found at construction from
+    the dofmap).  Lists in which consecutive cells are not neighbours, are neighbours the other way round, or are split
+    over the two launches (lcells / bcells) must give the same result: the action does not depend on the list order."""
+    import torch
+    import benchmark_dolfinx_b200 as bd
+    m, u, y_ref, _ = _cached(3, 1, "box")
+    cells = np.concatenate([m.lcells, m.bcells]).astype(np.int32)
+    rng = np.random.default_rng(3)
+    if order == "reversed":
+        lc, bc = cells[::-1].copy(), cells[:0].copy()
+    elif order == "shuffled":
+        lc, bc = rng.permutation(cells).astype(np.int32), cells[:0].copy()
+    else:  # a ragged cut in the middle of a z line, both parts in mesh order
+        cut = len(cells) // 2 + 3
+        lc, bc = cells[:cut].copy(), cells[cut:].copy()
+    mm = _Mesh(m, m.xgeom)
+    mm.lcells, mm.bcells = lc, bc
+    op = bd.MatFreeLaplacianGPU(mm, 3, 1, 2.0, dtype=dtype)
+    assert op.geometry_mode()[0] == "onthefly-brick" and "affine_pipe" in op.describe()
+    ud = torch.from_numpy(u.astype(dtype)).cuda()
+    for cap in (2, 0):
+        grid_cap(cap)
+        yd = torch.full_like(ud, 7.0)
+        op.apply(ud, yd)
+        torch.cuda.synchronize()
+        assert _rel(yd.cpu().numpy(), y_ref) < RTOL[dtype]
